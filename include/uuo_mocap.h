@@ -1,0 +1,161 @@
+/* uuo_mocap.h -- C-ABI of libuuomocap.so: the B200-native (sm_100a) SMPL marker-fitting hot path.
+ *
+ * Every entry point replaces a reference call site (paths relative to /root/reference); the
+ * reference has no FFI of its own (it is pure Python/PyTorch), so these are the functions a
+ * ctypes binding inside src/video_mocap/utils/smpl.py and src/video_mocap/optimization.py
+ * would bind.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative uuo_status on failure; uuo_last_error()
+ *     gives a thread-local message.  Nothing throws across the boundary.
+ *   - all tensor pointers are CALLER-OWNED DEVICE memory on the model's device, contiguous
+ *     row-major fp32 (indices int32) unless the parameter says "host".  The library owns only
+ *     the uuo_model constants.  Workspaces are caller-allocated (uuo_*_workspace_bytes).
+ *   - functions enqueue on `stream` (a cudaStream_t passed as void*) and return without
+ *     synchronising; a model is immutable after creation and may be shared across streams.
+ *   - there is no CPU fallback: without a CUDA device every compute call fails with
+ *     UUO_ERR_CUDA.
+ */
+#ifndef UUO_MOCAP_H
+#define UUO_MOCAP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct uuo_model uuo_model;
+
+enum uuo_status {
+  UUO_OK = 0,
+  UUO_ERR_ARG = -1,     /* bad argument (null pointer, bad size, unsupported shape) */
+  UUO_ERR_CUDA = -2,    /* a CUDA runtime call or kernel launch failed */
+  UUO_ERR_ALLOC = -3    /* device or host allocation failed */
+};
+
+/* How the pose arrays are to be read.
+ *   UUO_POSE_ROTMAT : [F,J,3,3] matrices used as they are        (smplx pose2rot=False,
+ *                     third_party/smplx/smplx/lbs.py:226-231)
+ *   UUO_POSE_AXISANGLE : [F,J,3] axis-angle through batch_rodrigues (pose2rot=True, lbs.py:218-225,299-333)
+ *   UUO_POSE_RAW6D  : [F,J,3,3] free 3x3 parameters re-orthonormalised by pytorch3d's
+ *                     rotation_6d_to_matrix(matrix_to_rotation_6d(X)) (rows 0,1 Gram-Schmidt) as
+ *                     the fitting closures do before every SMPL call
+ *                     (src/video_mocap/optimization.py:196-202,335-340), fused into the kernel. */
+enum uuo_pose_mode { UUO_POSE_ROTMAT = 0, UUO_POSE_AXISANGLE = 1, UUO_POSE_RAW6D = 2 };
+
+const char* uuo_last_error(void);
+int uuo_version(void);
+
+/* ---- model: replaces smplx.SMPL.__init__ buffer registration (body_models.py:144-269) ----
+ * HOST pointers: v_template[V,3], shapedirs[V,3,NB], posedirs[P,3V] (P = 9*(J-1), the layout
+ * smplx registers), J_regressor[J,V], lbs_weights[V,J], parents[J] (parents[0] = -1),
+ * extra_joint_ids[NE] (vertex_joint_selector.py:36-68).  Copies everything to `device`. */
+int uuo_model_create(const float* v_template, const float* shapedirs, const float* posedirs,
+                     const float* J_regressor, const float* lbs_weights, const int32_t* parents,
+                     const int32_t* extra_joint_ids, int V, int J, int NB, int P, int NE, int device,
+                     uuo_model** out);
+void uuo_model_destroy(uuo_model* m);
+/* what: 0=V 1=J 2=NB 3=P 4=NE 5=device 6=max nnz per skinning-weight row */
+int uuo_model_info(const uuo_model* m, int what);
+
+/* ---- SMPL layer: replaces smplx.SMPL.forward -> lbs() (body_models.py:315-399, lbs.py:156-252)
+ * and its autograd backward.  The workspace written by forward is what backward reads. */
+size_t uuo_lbs_workspace_bytes(const uuo_model* m, int F);
+
+/* betas[betas_rows,NB], betas_rows in {1,F} (1 = one row shared by all frames, body_models.py:371-376);
+ * global_orient[F,1,...], body_pose[F,J-1,...] per pose_mode; yaw[F] or NULL: when given the root
+ * matrix is Rz(yaw[f]) @ global_orient[f] (optimization.py:192,672-679) before pose_mode is applied;
+ * transl[F,3] or NULL.  Outputs vertices[F,V,3], joints[F,J+NE,3]. */
+int uuo_lbs_forward(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                    const float* body_pose, int pose_mode, const float* yaw, const float* transl, int F,
+                    float* vertices, float* joints, void* workspace, void* stream);
+
+/* g_vertices[F,V,3] / g_joints[F,J+NE,3] may be NULL (treated as zero).  Outputs (any may be NULL):
+ * g_betas[betas_rows,NB], g_global_orient / g_body_pose (shape of the inputs), g_yaw[F], g_transl[F,3].
+ * Inputs of the forward call must be passed again unchanged. */
+int uuo_lbs_backward(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                     const float* body_pose, int pose_mode, const float* yaw, int F,
+                     const float* g_vertices, const float* g_joints, void* workspace,
+                     float* g_betas, float* g_global_orient, float* g_body_pose, float* g_yaw,
+                     float* g_transl, void* stream);
+
+/* Backward for a gradient that touches only R vertex rows per frame (what the chamfer and marker
+ * losses produce): rows[F,R] vertex ids (or rows[R] when rows_shared), g_rows[F,R,3].  Same outputs
+ * as uuo_lbs_backward; never touches a dense [F,V,3] gradient. */
+int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                          const float* body_pose, int pose_mode, const float* yaw, int F,
+                          const int32_t* rows, int rows_shared, int R, const float* g_rows,
+                          const float* g_joints, void* workspace,
+                          float* g_betas, float* g_global_orient, float* g_body_pose, float* g_yaw,
+                          float* g_transl, void* stream);
+
+/* Forward of R selected vertices only (marker stage, optimization.py:345-351 is a gather):
+ * out_rows[F,R,3]; joints[F,J+NE,3] may be NULL. */
+int uuo_lbs_forward_rows(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                         const float* body_pose, int pose_mode, const float* yaw, const float* transl, int F,
+                         const int32_t* rows, int rows_shared, int R, float* out_rows, float* joints,
+                         void* workspace, void* stream);
+
+/* ---- correspondence: replaces pytorch3d knn_points(K=1) inside chamfer_distance as called by
+ * src/video_mocap/losses/chamfer_distance.py:5-21.  dist2[F,M] = min_v ((dx*dx+dy*dy)+dz*dz) with every
+ * operation rounded to fp32 (no FMA), idx[F,M] = the FIRST vertex attaining it. */
+int uuo_nn_argmin(const float* markers, const float* vertices, int F, int M, int V, float* dist2,
+                  int32_t* idx, void* stream);
+
+/* get_marker_mask (optimization.py:703-715): mask[F,M] = (|x|+|y|+|z| != 0) as float 0/1. */
+int uuo_marker_mask(const float* markers, int n_markers_total, float* mask, void* stream);
+
+/* weighted single-directional chamfer value and its gradient rows
+ * (chamfer_distance.py:5-21 + pytorch3d chamfer_distance weights / batch_reduction="mean"):
+ * loss_sum[0] += scale * sum_{f,m} w*d2 ; g_rows[F,M,3] = scale * w * (-2) * (marker - vertex[idx]),
+ * where the caller passes scale = weight / sum(w) (sum over ALL shards).
+ */
+int uuo_chamfer_rows(const float* markers, const float* vertices, const float* mask, const int32_t* idx,
+                     int F, int M, int V, float scale, float* loss_sum, float* g_rows, void* stream);
+
+/* MarkerLoss (src/video_mocap/losses/losses.py:43-51) on gathered rows virt[F,M,3]:
+ * loss_sum[0] += scale * sum (||m - v|| - dist)^2 * w ; g_virt[F,M,3] its gradient * scale. */
+int uuo_marker_loss_rows(const float* markers, const float* virt, const float* mask, int n, float dist,
+                         float scale, float* loss_sum, float* g_virt, void* stream);
+
+/* compute_nearest_points(use_mean) (optimization.py:464-486,595-603): acc[M,V] += sum over the
+ * frames with frame_mask==1 of ||vertex - marker||_2 (frames added in order), then
+ * uuo_mean_argmin divides by count and takes the first argmin per marker. */
+int uuo_mean_dist_accumulate(const float* markers, const float* vertices, const float* frame_mask, int F,
+                             int M, int V, float* acc, void* stream);
+int uuo_mean_argmin(const float* acc, int M, int V, float count, int32_t* idx, void* stream);
+
+/* ---- prior / regulariser terms of the closures (optimization.py:243-256,363-374) ----
+ * g[i] += scale * 2 * (x[i]-y[i]) ; loss_sum[0] += scale * sum (x-y)^2 (caller folds 1/numel in scale) */
+int uuo_sqdiff_accumulate(const float* x, const float* y, size_t n, float scale, float* loss_sum, float* g,
+                          void* stream);
+/* "temporal" term exactly as written (optimization.py:368-374): e_t = x[t+2] - 2 x[t+1] - x[t], x is
+ * [F,D] (one shard of the sequence).  prev2[2,D] = the two rows before row 0 and next2[2,D] = the two
+ * rows after row F-1 as received from the neighbouring shards (NULL at the ends of the sequence); with
+ * them every shard computes the full gradient of its own rows, so no gradient is sent back.  The shard
+ * adds to loss_sum the terms e_t whose t is one of its rows. */
+int uuo_temporal_accumulate(const float* x, const float* prev2, const float* next2, int F, int D, float scale,
+                            float* loss_sum, float* g, void* stream);
+/* mm[F,3] = mean over ALL M markers of the frame (optimization.py:248; dropped markers included). */
+int uuo_marker_mean(const float* markers, int F, int M, float* mm, void* stream);
+/* "trans_vel" (optimization.py:246-250): mse(trans[1:]-trans[:-1], mm[1:]-mm[:-1]).  prev[6] / next[6] =
+ * [trans(3), mm(3)] of the frame before row 0 / after row F-1 (NULL at the ends of the sequence). */
+int uuo_transvel_accumulate(const float* trans, const float* mm, const float* prev, const float* next, int F,
+                            float scale, float* loss_sum, float* g_trans, void* stream);
+
+/* ---- fused Adam over a flat parameter block (north-star optimiser; torch.optim.Adam semantics) */
+int uuo_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                  float beta1, float beta2, float eps, int step, void* stream);
+
+/* ---- measurement aid (bench.py): per-kernel CUDA-event timing on the launching stream.
+ * uuo_profile_enable(1) clears and starts recording, (0) stops.  uuo_profile_read(slot, ...) returns the
+ * number of slots; for a valid slot it waits for its events and reports the summed duration and count. */
+int uuo_profile_enable(int on);
+int uuo_profile_read(int slot, char* name, int name_cap, float* total_ms, int* count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UUO_MOCAP_H */

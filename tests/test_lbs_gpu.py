@@ -1,0 +1,148 @@
+"""Parity of the CUDA SMPL layer (through the C-ABI) against the oracle and the smplx golden vectors.
+
+Tolerances (BASELINE.json north_star): vertices / joints 1e-5 relative, gradients 1e-4 relative
+(relative to the largest magnitude of the reference tensor).
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL_OUT = 1e-5
+TOL_GRAD = 1e-4
+
+
+@pytest.fixture(scope="module")
+def layers(get_model):
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    from oracle.smpl_oracle import OracleSMPL
+    out = {}
+    for kind in ("dense", "top4"):
+        m = get_model(kind)
+        out[kind] = (SMPL(_as_struct(m), device="cuda:0"), OracleSMPL.from_model(m))
+    return out
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda().requires_grad_(True)
+
+
+@pytest.mark.parametrize("kind", ["dense", "top4"])
+@pytest.mark.parametrize("tag,pose2rot", [("rot", False), ("aa", True)])
+def test_against_smplx_golden(layers, golden, kind, tag, pose2rot):
+    """tests/golden/smplx_*.npz are outputs of the reference's own vendored smplx."""
+    smpl, _ = layers[kind]
+    g = golden(f"smplx_{kind}.npz")
+    go, bp = _cuda(g[f"{tag}_global_orient"]), _cuda(g[f"{tag}_body_pose"])
+    betas, transl = _cuda(g[f"{tag}_betas"]), _cuda(g[f"{tag}_transl"])
+    o = smpl(betas=betas, body_pose=bp, global_orient=go, transl=transl, pose2rot=pose2rot)
+    assert rel_err(o.vertices.detach().cpu(), g[f"{tag}_vertices"]) < TOL_OUT
+    assert rel_err(o.joints.detach().cpu(), g[f"{tag}_joints"]) < TOL_OUT
+    gv, gj = torch.from_numpy(g["g_vertices"]).cuda(), torch.from_numpy(g["g_joints"]).cuda()
+    ((o.vertices * gv).sum() + (o.joints * gj).sum()).backward()
+    for t, key in ((go, "g_global_orient"), (bp, "g_body_pose"), (betas, "g_betas"), (transl, "g_transl")):
+        ref = g[f"{tag}_{key}"]
+        assert rel_err(t.grad.cpu().numpy().reshape(ref.shape), ref) < TOL_GRAD, key
+
+
+def test_shared_betas_golden(layers, golden):
+    from uuo_mocap_b200 import synthetic
+    smpl, _ = layers["dense"]
+    g = golden("smplx_dense.npz")
+    mb = synthetic.make_lbs_microbench(g["rot_betas"].shape[0], seed=11)
+    rot = torch.from_numpy(mb["rot"]).cuda()
+    o = smpl(betas=torch.from_numpy(g["rot_betas"][:1]).cuda(), body_pose=rot[:, 1:], global_orient=rot[:, :1],
+             transl=torch.from_numpy(g["rot_transl"]).cuda(), pose2rot=False)
+    assert rel_err(o.vertices.cpu(), g["shared_vertices"]) < TOL_OUT
+    assert rel_err(o.joints.cpu(), g["shared_joints"]) < TOL_OUT
+
+
+@pytest.mark.parametrize("kind", ["dense", "top4"])
+@pytest.mark.parametrize("F", [1, 37, 130])
+@pytest.mark.parametrize("mode", ["rot", "aa", "raw6d_yaw"])
+@pytest.mark.parametrize("shared_betas", [False, True])
+def test_against_oracle(layers, kind, F, mode, shared_betas):
+    """Seeded inputs, ragged frame counts (not multiples of any tile), every pose mode."""
+    from uuo_mocap_b200 import synthetic
+    from uuo_mocap_b200.smpl import lbs_apply, POSE_RAW6D
+    from oracle import p3d_oracle as p3d
+    smpl, orc = layers[kind]
+    mb = synthetic.make_lbs_microbench(F, seed=100 + F)
+    rng = np.random.default_rng(F)
+    betas_np = mb["betas"][:1] if shared_betas else mb["betas"]
+    gv, gj = torch.from_numpy(mb["g_vertices"]), torch.from_numpy(mb["g_joints"])
+
+    def run(dev):
+        T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev).requires_grad_(True)
+        betas, transl = T(betas_np), T(mb["transl"])
+        leaves = [betas, transl]
+        if mode == "aa":
+            go, bp = T(mb["pose_aa"][:, :1]), T(mb["pose_aa"][:, 1:])
+            leaves += [go, bp]
+            if dev == "cpu":
+                o = orc.forward(betas, bp, go, transl, pose2rot=True)
+                v, j = o.vertices, o.joints
+            else:
+                o = smpl(betas=betas, body_pose=bp.reshape(F, -1), global_orient=go.reshape(F, -1), transl=transl,
+                         pose2rot=True)
+                v, j = o.vertices, o.joints
+        elif mode == "rot":
+            go, bp = T(mb["rot"][:, :1]), T(mb["rot"][:, 1:])
+            leaves += [go, bp]
+            if dev == "cpu":
+                o = orc.forward(betas, bp, go, transl, pose2rot=False)
+            else:
+                o = smpl(betas=betas, body_pose=bp, global_orient=go, transl=transl, pose2rot=False)
+            v, j = o.vertices, o.joints
+        else:
+            noise = np.random.default_rng(7).normal(0, 0.05, size=mb["rot"].shape).astype(np.float32)
+            raw = mb["rot"] + noise                       # free 3x3 parameters, not orthonormal
+            go, bp = T(raw[:, :1]), T(raw[:, 1:])
+            yaw = T(rng.normal(0, 0.5, size=(F, 1, 1)).astype(np.float32))
+            leaves += [go, bp, yaw]
+            if dev == "cpu":                              # optimization.py:192-202
+                z_root = p3d.compute_root_orient_z(yaw) @ go
+                o = orc.forward(betas, p3d.normalize_rot(bp), p3d.normalize_rot(z_root), transl, pose2rot=False)
+                v, j = o.vertices, o.joints
+            else:
+                v, j = lbs_apply(smpl.handle, betas, go, bp, transl, yaw, POSE_RAW6D)
+        ((v * gv.to(dev)).sum() + (j * gj.to(dev)).sum()).backward()
+        return v.detach().cpu().numpy(), j.detach().cpu().numpy(), [t.grad.cpu().numpy() for t in leaves]
+
+    v_ref, j_ref, g_ref = run("cpu")
+    v, j, g = run("cuda:0")
+    assert rel_err(v, v_ref) < TOL_OUT
+    assert rel_err(j, j_ref) < TOL_OUT
+    for a, b in zip(g, g_ref):
+        assert a.shape == b.shape
+        assert rel_err(a, b) < TOL_GRAD
+
+
+def test_partial_grads_and_errors(layers):
+    """Only joints used (g_vertices NULL), transl absent; error behaviour of SmplInference."""
+    from uuo_mocap_b200 import synthetic
+    from uuo_mocap_b200.smpl import SmplInference
+    smpl, orc = layers["top4"]
+    F = 5
+    mb = synthetic.make_lbs_microbench(F, seed=5)
+    res = []
+    for dev in ("cpu", "cuda:0"):
+        rot = torch.from_numpy(mb["rot"]).to(dev).requires_grad_(True)
+        betas = torch.from_numpy(mb["betas"]).to(dev).requires_grad_(True)
+        if dev == "cpu":
+            j = orc.forward(betas, rot[:, 1:], rot[:, :1], None, pose2rot=False).joints
+        else:
+            j = smpl(betas=betas, body_pose=rot[:, 1:], global_orient=rot[:, :1], pose2rot=False).joints
+        (j ** 2).sum().backward()
+        res.append((j.detach().cpu().numpy(), rot.grad.cpu().numpy(), betas.grad.cpu().numpy()))
+    for a, b in zip(res[1], res[0]):
+        assert rel_err(a, b) < TOL_GRAD
+    inf = SmplInference("cuda:0", model=smpl)
+    with pytest.raises(ValueError, match="Betas array must have 10 beta values"):
+        inf(poses=torch.zeros(1, 23, 3, 3).cuda(), betas=torch.zeros(1, 9).cuda(),
+            root_orient=torch.zeros(1, 1, 3, 3).cuda(), trans=torch.zeros(1, 3).cuda())
+    assert inf.get_lbs_weights().shape == (6890, 24)
+    assert inf.smpl.parents.shape == (24,)

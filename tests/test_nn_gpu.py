@@ -1,0 +1,74 @@
+"""Correspondence kernels against the oracle: indices and squared distances BIT-EXACT."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _clouds(F, M, V, seed, ties=False):
+    rng = np.random.default_rng(seed)
+    v = rng.normal(0, 0.5, size=(F, V, 3)).astype(np.float32)
+    m = rng.normal(0, 0.5, size=(F, M, 3)).astype(np.float32)
+    if ties:   # duplicated vertices + coarse grid -> many exact ties, first index must win
+        v = np.round(v * 4) / 4
+        m = np.round(m * 4) / 4
+        v[:, V // 2:] = v[:, : V - V // 2]
+    return torch.from_numpy(m), torch.from_numpy(v)
+
+
+@pytest.mark.parametrize("F,M,V", [(1, 1, 1), (3, 41, 6890), (5, 45, 6890), (2, 7, 19), (2, 300, 515), (4, 256, 1000)])
+@pytest.mark.parametrize("ties", [False, True])
+def test_nn_argmin_bit_exact(F, M, V, ties):
+    from uuo_mocap_b200 import ops
+    from oracle import p3d_oracle as p3d
+    m, v = _clouds(F, M, V, seed=F * 1000 + M, ties=ties)
+    d_ref, i_ref = p3d.knn_k1(m, v)
+    d, i = ops.nn_argmin(m.cuda(), v.cuda())
+    assert torch.equal(i.cpu().long(), i_ref)
+    assert torch.equal(d.cpu(), d_ref)
+
+
+def test_nn_dropped_markers_and_mask():
+    from uuo_mocap_b200 import ops
+    from oracle import closures, p3d_oracle as p3d
+    m, v = _clouds(6, 41, 6890, seed=5)
+    m[::2, ::3] = 0.0
+    mask = ops.get_marker_mask(m.cuda())
+    assert torch.equal(mask.cpu() != 0, closures.get_marker_mask(m))
+    d_ref, i_ref = p3d.knn_k1(m, v)
+    d, i = ops.nn_argmin(m.cuda(), v.cuda())
+    assert torch.equal(i.cpu().long(), i_ref) and torch.equal(d.cpu(), d_ref)
+
+
+def test_chamfer_smoke_seed(golden):
+    """The reference's only deterministic seed (losses/chamfer_distance.py:24-36) through the CUDA path."""
+    from uuo_mocap_b200 import ops
+    x = torch.arange(0, 16 * 7 * 3, dtype=torch.float32).reshape(16, 7, 3)
+    y = torch.arange(0, 16 * 19 * 3, dtype=torch.float32).reshape(16, 19, 3)
+    w = torch.ones(16, 7)
+    w[:, ::2] = 0
+    d, _ = ops.nn_argmin(x.cuda(), y.cuda())
+    val = float((d.cpu().reshape(-1) * w.reshape(-1)).sum() / w.sum())
+    ref = float(golden("closure_top4.npz")["smoke_weighted_chamfer"])
+    assert abs(val - ref) <= 1e-6 * abs(ref)
+
+
+def test_mean_distance_argmin(get_model):
+    from uuo_mocap_b200 import ops
+    rng = np.random.default_rng(3)
+    F, M, V = 9, 13, 700
+    v = rng.normal(0, 0.5, size=(F, V, 3)).astype(np.float32)
+    m = rng.normal(0, 0.5, size=(F, M, 3)).astype(np.float32)
+    fm = np.ones(F, dtype=np.float32)
+    fm[[2, 5]] = 0
+    sel = np.where(fm == 1)[0]
+    acc = np.zeros((M, V), dtype=np.float32)
+    for f in sel:   # optimization.py:479-486,596-599 (numpy fp32, frames added in order)
+        acc += np.linalg.norm(v[f][None, :, :] - m[f][:, None, :], axis=-1)
+    mean = acc / np.float32(len(sel))
+    idx_ref = np.argmin(mean, axis=-1)
+    idx, acc_gpu = ops.mean_distance_argmin(torch.from_numpy(m).cuda(), torch.from_numpy(v).cuda(),
+                                            torch.from_numpy(fm).cuda())
+    assert np.array_equal(acc_gpu.cpu().numpy(), acc)
+    assert np.array_equal(idx.cpu().numpy().astype(np.int64), idx_ref)

@@ -1,0 +1,161 @@
+// Model constants: host-side folding and upload.  Replaces the buffer registration of
+// smplx.SMPL.__init__ (third_party/smplx/smplx/body_models.py:144-269).
+#include <stdarg.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void uuo_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* uuo_last_error(void) { return g_err; }
+extern "C" int uuo_version(void) { return 100; }
+
+template <typename T>
+static int upload(T** dst, const std::vector<T>& src) {
+  UUO_CUDA(cudaMalloc((void**)dst, src.size() * sizeof(T)));
+  UUO_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return UUO_OK;
+}
+
+extern "C" int uuo_model_create(const float* v_template, const float* shapedirs, const float* posedirs,
+                                const float* J_regressor, const float* lbs_weights, const int32_t* parents,
+                                const int32_t* extra_joint_ids, int V, int J, int NB, int P, int NE,
+                                int device, uuo_model** out) {
+  UUO_CHECK_ARG(out != nullptr, "out is NULL");
+  *out = nullptr;
+  UUO_CHECK_ARG(v_template && shapedirs && posedirs && J_regressor && lbs_weights && parents, "NULL array");
+  UUO_CHECK_ARG(V > 0 && V < (1 << 24), "bad V");
+  UUO_CHECK_ARG(J == UUO_SKIN_J, "this build supports J == 24 (SMPL) only");
+  UUO_CHECK_ARG(P == 9 * (J - 1), "P must be 9*(J-1)");
+  UUO_CHECK_ARG(NB >= 1 && NB <= 16, "NB must be in [1,16]");
+  UUO_CHECK_ARG(NE >= 0 && (NE == 0 || extra_joint_ids), "bad extra joints");
+  UUO_CHECK_ARG(parents[0] < 0, "parents[0] must be -1");
+  for (int j = 1; j < J; ++j) UUO_CHECK_ARG(parents[j] >= 0 && parents[j] < j, "parents must precede children");
+  for (int e = 0; e < NE; ++e) UUO_CHECK_ARG(extra_joint_ids[e] >= 0 && extra_joint_ids[e] < V, "extra joint id out of range");
+
+  int ndev = 0;
+  UUO_CUDA(cudaGetDeviceCount(&ndev));
+  UUO_CHECK_ARG(device >= 0 && device < ndev, "no such CUDA device");
+  UUO_CUDA(cudaSetDevice(device));
+
+  uuo_model* m = new (std::nothrow) uuo_model();
+  if (!m) { uuo_set_error("uuo_model_create: host allocation failed"); return UUO_ERR_ALLOC; }
+  memset(m, 0, sizeof(*m));
+  m->V = V; m->J = J; m->NB = NB; m->P = P; m->NE = NE; m->device = device;
+  m->KC = P + NB;
+  m->KP = (m->KC + 15) / 16 * 16;
+  m->NP = (3 * V + 127) / 128 * 128;
+  const int KP = m->KP, NP = m->NP, N = 3 * V;
+
+  // kinematic tree tables
+  memset(m->children, -1, sizeof(m->children));
+  int nchild[UUO_MAX_J] = {0};
+  m->max_depth = 0;
+  for (int j = 0; j < UUO_MAX_J; ++j) { m->parents[j] = -1; m->depth[j] = 0; }
+  for (int j = 1; j < J; ++j) {
+    int p = parents[j];
+    m->parents[j] = (int8_t)p;
+    m->depth[j] = (int8_t)(m->depth[p] + 1);
+    m->max_depth = std::max(m->max_depth, (int)m->depth[j]);
+    if (nchild[p] >= UUO_MAX_CHILD) {
+      delete m;
+      uuo_set_error("uuo_model_create: joint %d has more than %d children", p, UUO_MAX_CHILD);
+      return UUO_ERR_ARG;
+    }
+    m->children[p][nchild[p]++] = (int8_t)j;
+  }
+
+  std::vector<float> vt(NP, 0.f), Bmat((size_t)KP * NP, 0.f), Bt((size_t)NP * KP, 0.f);
+  for (int n = 0; n < N; ++n) vt[n] = v_template[n];
+  for (int p = 0; p < P; ++p)
+    for (int n = 0; n < N; ++n) Bmat[(size_t)p * NP + n] = posedirs[(size_t)p * N + n];
+  for (int n = 0; n < N; ++n)
+    for (int l = 0; l < NB; ++l) Bmat[(size_t)(P + l) * NP + n] = shapedirs[(size_t)n * NB + l];
+  for (int k = 0; k < KP; ++k)
+    for (int n = 0; n < NP; ++n) Bt[(size_t)n * KP + k] = Bmat[(size_t)k * NP + n];
+
+  // fold the joint regressor (lbs.py:209-213): J = Jreg @ (v_template + shapedirs . beta)
+  std::vector<float> J0((size_t)J * 3), Jdirs((size_t)J * 3 * NB);
+  for (int j = 0; j < J; ++j)
+    for (int k = 0; k < 3; ++k) {
+      double a = 0.0;
+      for (int v = 0; v < V; ++v) a += (double)J_regressor[(size_t)j * V + v] * v_template[v * 3 + k];
+      J0[j * 3 + k] = (float)a;
+      for (int l = 0; l < NB; ++l) {
+        double s = 0.0;
+        for (int v = 0; v < V; ++v)
+          s += (double)J_regressor[(size_t)j * V + v] * shapedirs[((size_t)v * 3 + k) * NB + l];
+        Jdirs[(j * 3 + k) * NB + l] = (float)s;
+      }
+    }
+
+  std::vector<float> W((size_t)V * J);
+  std::vector<int32_t> ell_j((size_t)V * 4, 0);
+  std::vector<float> ell_w((size_t)V * 4, 0.f);
+  m->max_nnz = 0;
+  for (int v = 0; v < V; ++v) {
+    int nnz = 0;
+    for (int j = 0; j < J; ++j) {
+      float w = lbs_weights[(size_t)v * J + j];
+      W[(size_t)v * J + j] = w;
+      if (w != 0.f) {
+        if (nnz < 4) { ell_j[v * 4 + nnz] = j; ell_w[v * 4 + nnz] = w; }
+        ++nnz;
+      }
+    }
+    m->max_nnz = std::max(m->max_nnz, nnz);
+  }
+  std::vector<uint8_t> vflag(V, 0);
+  std::vector<int32_t> ex(std::max(NE, 1), 0);
+  for (int e = 0; e < NE; ++e) { ex[e] = extra_joint_ids[e]; vflag[ex[e]] = 1; }
+
+  int rc = UUO_OK;
+  if ((rc = upload(&m->vt, vt)) || (rc = upload(&m->Bmat, Bmat)) || (rc = upload(&m->Bt, Bt)) ||
+      (rc = upload(&m->J0, J0)) || (rc = upload(&m->Jdirs, Jdirs)) || (rc = upload(&m->W, W)) ||
+      (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
+      (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag))) {
+    uuo_model_destroy(m);
+    return rc;
+  }
+  *out = m;
+  return UUO_OK;
+}
+
+extern "C" void uuo_model_destroy(uuo_model* m) {
+  if (!m) return;
+  cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
+  cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
+  delete m;
+}
+
+extern "C" int uuo_model_info(const uuo_model* m, int what) {
+  if (!m) return UUO_ERR_ARG;
+  switch (what) {
+    case 0: return m->V;
+    case 1: return m->J;
+    case 2: return m->NB;
+    case 3: return m->P;
+    case 4: return m->NE;
+    case 5: return m->device;
+    case 6: return m->max_nnz;
+    case 7: return m->KP;
+    case 8: return m->NP;
+    default: return UUO_ERR_ARG;
+  }
+}
+
+extern "C" size_t uuo_lbs_workspace_bytes(const uuo_model* m, int F) {
+  if (!m || F <= 0) return 0;
+  uuo_ws w = carve_ws(m, F, nullptr);
+  return w.total_floats * sizeof(float);
+}

@@ -1,0 +1,109 @@
+"""Tensor-level wrappers of the correspondence / loss / optimiser entry points of libuuomocap.
+
+Each function mirrors a reference call site (cited) and is one C-ABI call on the current CUDA
+stream.  Inputs must be CUDA tensors; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+MARKER_DISTANCE = 0.0095   # /root/reference/src/video_mocap/utils/settings.py:1
+
+
+def _req(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise _lib.UuoError("%s must be a CUDA tensor (uuo-mocap_b200 has no CPU path)" % name)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def nn_argmin(markers: torch.Tensor, vertices: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """pytorch3d knn_points(K=1) as used by chamfer_distance
+    (src/video_mocap/losses/chamfer_distance.py:5-21): markers [F,M,3], vertices [F,V,3]
+    -> (dist2 [F,M] fp32, idx [F,M] int32; first minimum wins)."""
+    markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
+    F, M, _ = markers.shape
+    V = vertices.shape[1]
+    if vertices.shape[0] != F:
+        raise ValueError("markers and vertices must have the same number of frames")
+    d = torch.empty((F, M), dtype=torch.float32, device=markers.device)
+    i = torch.empty((F, M), dtype=torch.int32, device=markers.device)
+    with torch.cuda.device(markers.device):
+        check(_lib.lib().uuo_nn_argmin(ptr(markers), ptr(vertices), F, M, V, ptr(d), ptr(i),
+                                       stream_ptr(markers.device)))
+    return d, i
+
+
+def get_marker_mask(markers: torch.Tensor) -> torch.Tensor:
+    """src/video_mocap/optimization.py:703-715 (float 0/1 instead of bool)."""
+    markers = _req(markers, "markers")
+    mask = torch.empty(markers.shape[:-1], dtype=torch.float32, device=markers.device)
+    with torch.cuda.device(markers.device):
+        check(_lib.lib().uuo_marker_mask(ptr(markers), mask.numel(), ptr(mask), stream_ptr(markers.device)))
+    return mask
+
+
+def mean_distance_argmin(markers: torch.Tensor, vertices: torch.Tensor, frame_mask: Optional[torch.Tensor] = None,
+                         acc: Optional[torch.Tensor] = None, finalize: bool = True, count: Optional[float] = None):
+    """compute_nearest_points(use_mean) (optimization.py:464-486,595-603): returns (idx [M] int32, acc [M,V]).
+    With ``finalize=False`` only accumulates (frame-range shards all-reduce ``acc`` and the count, then
+    call again with F=0 frames or use ``mean_argmin``)."""
+    markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
+    F, M, _ = markers.shape
+    V = vertices.shape[1]
+    dev = markers.device
+    if acc is None:
+        acc = torch.zeros((M, V), dtype=torch.float32, device=dev)
+    fm = _req(frame_mask, "frame_mask") if frame_mask is not None else None
+    with torch.cuda.device(dev):
+        check(_lib.lib().uuo_mean_dist_accumulate(ptr(markers), ptr(vertices), ptr(fm), F, M, V, ptr(acc),
+                                                  stream_ptr(dev)))
+    if not finalize:
+        return None, acc
+    if count is None:
+        count = float(F if fm is None else int((fm == 1).sum().item()))
+    return mean_argmin(acc, max(count, 1.0)), acc
+
+
+def mean_argmin(acc: torch.Tensor, count: float) -> torch.Tensor:
+    acc = _req(acc, "acc")
+    M, V = acc.shape
+    idx = torch.empty((M,), dtype=torch.int32, device=acc.device)
+    with torch.cuda.device(acc.device):
+        check(_lib.lib().uuo_mean_argmin(ptr(acc), M, V, float(count), ptr(idx), stream_ptr(acc.device)))
+    return idx
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, betas=(0.9, 0.999), eps=1e-8):
+    """torch.optim.Adam single-tensor update, in place, one fused kernel over the flat block."""
+    for t in (param, grad, exp_avg, exp_avg_sq):
+        if not (t.is_cuda and t.is_contiguous() and t.dtype == torch.float32):
+            raise _lib.UuoError("adam_step needs contiguous fp32 CUDA tensors")
+    with torch.cuda.device(param.device):
+        check(_lib.lib().uuo_adam_step(ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(),
+                                       float(lr), float(betas[0]), float(betas[1]), float(eps), int(step),
+                                       stream_ptr(param.device)))
+
+
+def profile_enable(on: bool):
+    check(_lib.lib().uuo_profile_enable(1 if on else 0))
+
+
+def profile_read():
+    """{kernel name: (total_ms, launches)} of the scopes recorded since profile_enable(True)."""
+    import ctypes as C
+    l = _lib.lib()
+    out = {}
+    n = l.uuo_profile_read(-1, None, 0, None, None)
+    for s in range(n):
+        name = C.create_string_buffer(64)
+        ms, cnt = C.c_float(0), C.c_int(0)
+        l.uuo_profile_read(s, name, 64, C.byref(ms), C.byref(cnt))
+        out[name.value.decode()] = (ms.value, cnt.value)
+    return out
