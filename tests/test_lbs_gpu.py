@@ -73,6 +73,7 @@ def test_against_oracle(layers, kind, F, mode, shared_betas):
     mb = synthetic.make_lbs_microbench(F, seed=100 + F)
     rng = np.random.default_rng(F)
     betas_np = mb["betas"][:1] if shared_betas else mb["betas"]
+    yaw_np = rng.normal(0, 0.5, size=(F, 1, 1)).astype(np.float32)
     gv, gj = torch.from_numpy(mb["g_vertices"]), torch.from_numpy(mb["g_joints"])
 
     def run(dev):
@@ -101,7 +102,7 @@ def test_against_oracle(layers, kind, F, mode, shared_betas):
             noise = np.random.default_rng(7).normal(0, 0.05, size=mb["rot"].shape).astype(np.float32)
             raw = mb["rot"] + noise                       # free 3x3 parameters, not orthonormal
             go, bp = T(raw[:, :1]), T(raw[:, 1:])
-            yaw = T(rng.normal(0, 0.5, size=(F, 1, 1)).astype(np.float32))
+            yaw = T(yaw_np)
             leaves += [go, bp, yaw]
             if dev == "cpu":                              # optimization.py:192-202
                 z_root = p3d.compute_root_orient_z(yaw) @ go

@@ -295,11 +295,11 @@ __global__ void __launch_bounds__(128) fk_backward_kernel(
   for (int c = 0; c < 3; ++c)
     gJr[c] = act ? -(s.RG[c] * gAm[3] + s.RG[3 + c] * gAm[7] + s.RG[6 + c] * gAm[11]) : 0.f;
 
-  // g_transl = sum_v g_vertices (partials, lanes 0..2) + sum over ALL output joints of g_joints
+  // g_transl = sum_v g_vertices incl. extra-joint rows (partials, lanes 0..2) + sum over the J posed joints of g_joints
   if (g_transl) {
     float tj[3] = {0.f, 0.f, 0.f};
     if (g_joints) {
-      for (int q = lane; q < n_joints_out; q += 32) {
+      for (int q = lane; q < J; q += 32) {   // extra joints are vertices: already inside the vertex partials
         const float* gq = g_joints + ((size_t)f * n_joints_out + q) * 3;
         tj[0] += gq[0]; tj[1] += gq[1]; tj[2] += gq[2];
       }

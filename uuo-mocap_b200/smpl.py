@@ -67,9 +67,12 @@ class ModelHandle:
 
     def __del__(self):
         h = getattr(self, "handle", None)
-        if h is not None and _lib._lib is not None:
-            _lib._lib.uuo_model_destroy(h)
-            self.handle = None
+        try:
+            if h is not None and _lib is not None and _lib._lib is not None:
+                _lib._lib.uuo_model_destroy(h)
+                self.handle = None
+        except Exception:   # interpreter shutdown
+            pass
 
     def workspace(self, F: int) -> torch.Tensor:
         n = _lib.lib().uuo_lbs_workspace_bytes(self.handle, F)
