@@ -1,0 +1,175 @@
+"""Fitting-loop parity: CUDA closures (loss, correspondences, every gradient) against the oracle closures
+and their golden vectors; fused Adam against torch.optim.Adam on the oracle closure (end-point RMSE)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx(get_model):
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    from oracle.smpl_oracle import OracleSMPL
+    m = get_model("top4")
+    return m, SMPL(_as_struct(m), device="cuda:0"), OracleSMPL.from_model(m)
+
+
+def _T(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def test_chamfer_closure_golden(ctx, golden):
+    """closure_stage_chamfer incl. the optional trans_vel term: loss 1e-5, idx exact, grads 1e-4."""
+    from uuo_mocap_b200.fit import FitProblem, ParamBlock, chamfer_closure
+    _, smpl, _ = ctx
+    g = golden("closure_top4.npz")
+    F = g["markers"].shape[0]
+    prob = FitProblem(smpl, _T(g["markers"]), _T(g["ch_o_pose"]), _T(g["ch_o_betas"]))
+    pb = ParamBlock.build({"trans": _T(g["ch_trans"]), "z_angle": _T(g["ch_z"]).reshape(F), "betas": _T(g["ch_betas"]),
+                           "pose_body": _T(g["ch_pose"])}, "cuda:0")
+    losses = {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0, "trans_vel": 1.0}
+    loss = chamfer_closure(prob, pb, _T(g["ch_root"]).cuda(), losses)
+    assert abs(float(loss) - float(g["ch_loss"])) <= 1e-5 * abs(float(g["ch_loss"]))
+    assert np.array_equal(prob.idx.cpu().numpy().astype(np.int64), g["ch_idx"])
+    for k, ref in (("pose_body", "ch_g_pose"), ("betas", "ch_g_betas"), ("trans", "ch_g_trans"), ("z_angle", "ch_g_z")):
+        got = pb.gviews[k].cpu().numpy().reshape(g[ref].shape)
+        assert rel_err(got, g[ref]) < 1e-4, k
+
+
+def test_marker_closure_golden(ctx, golden):
+    from uuo_mocap_b200.fit import FitProblem, ParamBlock, marker_closure
+    _, smpl, _ = ctx
+    g = golden("closure_top4.npz")
+    prob = FitProblem(smpl, _T(g["markers"]), _T(g["ch_o_pose"]), _T(g["ch_o_betas"]))
+    pb = ParamBlock.build({"pose_body": _T(g["ch_pose"]), "betas": _T(g["ch_betas"]), "root_orient": _T(g["mk_root"]),
+                           "trans": _T(g["ch_trans"])}, "cuda:0")
+    losses = {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0, "temporal": 1.0}
+    loss = marker_closure(prob, pb, _T(g["mk_vidx"]).to(torch.int32).cuda(), losses)
+    assert abs(float(loss) - float(g["mk_loss"])) <= 1e-5 * abs(float(g["mk_loss"]))
+    for k, ref in (("pose_body", "mk_g_pose"), ("betas", "mk_g_betas"), ("trans", "mk_g_trans"), ("root_orient", "mk_g_root")):
+        got = pb.gviews[k].cpu().numpy().reshape(g[ref].shape)
+        assert rel_err(got, g[ref]) < 1e-4, k
+
+
+def test_compute_nearest_points(ctx, golden):
+    from uuo_mocap_b200.fit import compute_nearest_points
+    from oracle import closures
+    _, smpl, orc = ctx
+    g = golden("closure_top4.npz")
+    mk, pose, betas, root, trans = (_T(g[k]) for k in ("markers", "ch_pose", "ch_betas", "mk_root", "ch_trans"))
+    F = mk.shape[0]
+    img_mask = torch.ones(F)
+    img_mask[1] = 0
+    idx_ref, mean_ref = closures.mean_distance_argmin(orc, mk, pose, betas, root, trans, img_mask)
+    one_hot = compute_nearest_points(mk, pose.cuda(), betas.cuda(), root.cuda(), trans.cuda(), smpl, img_mask=img_mask)
+    assert one_hot.shape == (mk.shape[1], 6890) and float(one_hot.sum()) == mk.shape[1]
+    idx = torch.argmax(one_hot, dim=1).cpu().numpy()
+    # vertices differ from the oracle's by ~1e-7: allow a different pick only on a near-tie
+    for m in np.where(idx != idx_ref)[0]:
+        assert abs(mean_ref[m, idx[m]] - mean_ref[m, idx_ref[m]]) <= 1e-6 * mean_ref[m, idx_ref[m]]
+    assert (idx == idx_ref).mean() > 0.9
+
+
+def _setup_fit(ctx, F, seed, n_ghost=2, dropout=0.1):
+    from uuo_mocap_b200 import synthetic
+    model, smpl, orc = ctx
+    cap = synthetic.make_capture(model, F, num_markers=41, seed=seed, n_ghost=n_ghost, dropout_p=dropout, dropout_block=2,
+                                 prior_pose_noise=0.05, prior_trans_err=0.03, prior_yaw_err=0.1)
+    return cap
+
+
+def test_adam_fit_matches_oracle_adam(ctx):
+    """Fixed iteration count, same init / lr: fused Adam on the CUDA closure vs torch.optim.Adam on the oracle
+    closure (CPU).  Final fitted marker RMSE within 0.5 mm (BASELINE.json north_star)."""
+    from uuo_mocap_b200 import fit
+    from oracle import closures
+    model, smpl, orc = ctx
+    F, iters, lr = 10, 25, 0.01
+    cap = _setup_fit(ctx, F, seed=31)
+    mk = _T(cap.markers)
+    cfg = fit.default_config(num_iters=iters, optimizer="adam", lr=lr)
+
+    def init():
+        return (_T(cap.prior_pose_body).clone(), _T(cap.prior_betas).clone(), _T(cap.prior_root_orient).clone(),
+                _T(cap.prior_trans).clone())
+    o_pose, o_betas = _T(cap.prior_pose_body), _T(cap.prior_betas)
+
+    # ---- oracle: chamfer stage -> correspondences -> marker stage
+    pose, betas, root, trans = [t.requires_grad_(True) for t in init()]
+    root.requires_grad_(False)
+    z = torch.zeros(F, 1, 1, requires_grad=True)
+    lc = cfg["stages"]["chamfer"]["losses"]
+    closures.run_adam([trans, z, betas, pose],
+                      lambda: closures.chamfer_stage_loss(orc, mk, pose, o_pose, betas, o_betas, root, trans, z, lc), iters, lr)
+    from oracle import p3d_oracle as p3d
+    with torch.no_grad():
+        root = (p3d.compute_root_orient_z(z) @ root).detach()
+    vidx_ref, _ = closures.mean_distance_argmin(orc, mk, pose.detach(), betas.detach(), root, trans.detach(), torch.ones(F))
+    root.requires_grad_(True)
+    lm = cfg["stages"]["marker"]["losses"]
+    closures.run_adam([pose, betas, root, trans],
+                      lambda: closures.marker_stage_loss(orc, mk, pose, o_pose, betas, o_betas, root, trans,
+                                                         torch.from_numpy(vidx_ref), lm), iters, lr)
+
+    def rmse(orc_pose, orc_betas, orc_root, orc_trans, vidx):
+        with torch.no_grad():
+            v = orc.forward(orc_betas, p3d.normalize_rot(orc_pose), p3d.normalize_rot(orc_root), orc_trans, pose2rot=False).vertices
+        d = torch.norm(mk - v[:, vidx], dim=-1)
+        w = closures.get_marker_mask(mk).float()
+        return float(torch.sqrt((w * (d - closures.MARKER_DISTANCE) ** 2).sum() / w.sum()))
+    rmse_ref = rmse(pose.detach(), betas.detach(), root.detach(), trans.detach(), torch.from_numpy(vidx_ref))
+
+    # ---- CUDA path through the reference's stage functions
+    c_pose, c_betas, c_root, c_trans = [t.cuda() for t in init()]
+    fit.optim_chamfer(mk, c_pose, o_pose, c_betas, o_betas, c_root, c_trans, torch.ones(F), None, smpl, cfg)
+    one_hot = fit.compute_nearest_points(mk, c_pose, c_betas, c_root, c_trans, smpl, img_mask=torch.ones(F), config=cfg)
+    fit.optim_markers(mk, c_pose, o_pose, c_betas, o_betas, c_root, c_trans, one_hot, torch.ones(F), smpl, cfg)
+    vidx = torch.argmax(one_hot, dim=1).cpu()
+    rmse_gpu = rmse(c_pose.cpu(), c_betas.cpu(), c_root.cpu(), c_trans.cpu(), vidx)
+    assert abs(rmse_gpu - rmse_ref) < 0.5e-3, (rmse_gpu, rmse_ref)
+    assert (vidx.numpy() == vidx_ref).mean() > 0.9
+    assert rel_err(c_trans.cpu().numpy(), trans.detach().numpy()) < 1e-3
+    assert rel_err(c_betas.cpu().numpy(), betas.detach().numpy()) < 1e-2
+
+
+def test_lbfgs_drives_the_cuda_closure(ctx):
+    """The reference's optimiser (torch LBFGS, strong Wolfe) over the CUDA closure: the loss must go down."""
+    from uuo_mocap_b200 import fit
+    model, smpl, orc = ctx
+    F = 8
+    cap = _setup_fit(ctx, F, seed=33)
+    cfg = fit.default_config(num_iters=8, optimizer="lbfgs")
+    mk = _T(cap.markers)
+    pose, betas, root, trans = (_T(cap.prior_pose_body).cuda(), _T(cap.prior_betas).cuda(),
+                                _T(cap.prior_root_orient).cuda(), _T(cap.prior_trans).cuda())
+    o_pose, o_betas = _T(cap.prior_pose_body), _T(cap.prior_betas)
+    prob = fit.FitProblem(smpl, mk, o_pose, o_betas)
+    pb = fit.ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F), "betas": betas, "pose_body": pose}, "cuda:0")
+    l0 = float(fit.chamfer_closure(prob, pb, root, cfg["stages"]["chamfer"]["losses"]))
+    fit.optim_chamfer(mk, pose, o_pose, betas, o_betas, root, trans, None, None, smpl, cfg)
+    pb = fit.ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F), "betas": betas, "pose_body": pose}, "cuda:0")
+    l1 = float(fit.chamfer_closure(prob, pb, root, cfg["stages"]["chamfer"]["losses"]))
+    assert l1 < l0
+
+
+def test_stacked_hypotheses_equal_separate_fits(ctx):
+    """MHT batched along the frame axis == the same hypotheses fitted one after the other (multimodal.py:462-574)."""
+    from uuo_mocap_b200 import fit
+    model, smpl, orc = ctx
+    F, H = 6, 3
+    cap = _setup_fit(ctx, F, seed=35, n_ghost=0, dropout=0.0)
+    cfg = fit.default_config(num_iters=6, optimizer="adam", lr=0.01)
+    mk = _T(cap.markers)
+    o_pose, o_betas = _T(cap.prior_pose_body), _T(cap.prior_betas)
+    args = (mk, _T(cap.prior_pose_body), o_pose, _T(cap.prior_betas), o_betas, _T(cap.prior_root_orient), _T(cap.prior_trans),
+            torch.ones(F), smpl, cfg)
+    angles = [0.0, 2 * np.pi / 3, 4 * np.pi / 3]
+    best, scores, fitted = fit.fit_hypotheses(*args, angles=angles)
+    for h, a in enumerate(angles):
+        b1, s1, f1 = fit.fit_hypotheses(*args, angles=[a])
+        assert abs(s1[0] - scores[h]) <= 1e-4 * abs(s1[0])
+        assert rel_err(fitted[h]["trans"].cpu().numpy(), f1[0]["trans"].cpu().numpy()) < 1e-4
+    assert best == int(np.argmin(scores))

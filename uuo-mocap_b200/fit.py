@@ -1,0 +1,503 @@
+"""The video_mocap.yaml fitting loop on the CUDA path: stage closures, Adam / L-BFGS drivers and the
+reference's stage functions (same names and argument meaning as
+/root/reference/src/video_mocap/optimization.py).
+
+A closure evaluation is a fixed sequence of C-ABI calls, no autograd graph and no [F,M,V] tensor:
+  chamfer stage (optimization.py:187-275):
+      uuo_lbs_forward(RAW6D, yaw) -> uuo_nn_argmin -> uuo_chamfer_rows -> uuo_lbs_backward_rows
+      -> uuo_sqdiff_accumulate (video-pose prior, betas prior) [-> uuo_transvel_accumulate]
+  marker stage (optimization.py:329-394):
+      uuo_lbs_forward_rows -> uuo_marker_loss_rows -> uuo_lbs_backward_rows -> priors [-> uuo_temporal_accumulate]
+followed by uuo_adam_step over the flat parameter block (north-star optimiser) or torch.optim.LBFGS
+(the reference's optimiser) driving the same closure.
+
+Frame-range sharding (``Shard``): every rank owns a contiguous frame range; per iteration the ranks
+all-reduce ONE 16-float buffer (d/d betas + loss) and, only when a temporal term is enabled, exchange
+a 1- or 2-frame halo with their neighbours (torch.distributed P2P: NCCL over NVLink on GPUs, gloo in
+the CPU tests).  All ``mean`` normalisers use GLOBAL counts.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+from ._lib import check, ptr, stream_ptr
+from .dist import Shard, exchange_halo
+from .smpl import POSE_RAW6D, SMPL, SmplInference
+
+MARKER_DISTANCE = ops.MARKER_DISTANCE
+
+
+def _model_of(smpl_inference) -> SMPL:
+    return smpl_inference.smpl if isinstance(smpl_inference, SmplInference) else smpl_inference
+
+
+class FitProblem:
+    """Device buffers of one shard of one sequence (or of H hypotheses stacked along the frame axis)."""
+
+    def __init__(self, smpl_inference, markers: torch.Tensor, o_pose_body: torch.Tensor, o_betas: torch.Tensor,
+                 shard: Optional[Shard] = None, groups: int = 1):
+        self.smpl = _model_of(smpl_inference)
+        self.mh = self.smpl.handle
+        dev = self.mh.device
+        self.dev = dev
+        self.shard = shard or Shard()
+        self.groups = groups                              # hypotheses stacked along frames (MHT)
+        self.markers = markers.to(dev, torch.float32).contiguous()
+        self.F, self.M = self.markers.shape[:2]
+        if self.F % groups:
+            raise ValueError("frames must divide evenly into hypothesis groups")
+        self.o_pose_body = o_pose_body.to(dev, torch.float32).contiguous()
+        self.o_betas = o_betas.to(dev, torch.float32).reshape(-1, self.mh.NB).contiguous()
+        self.mask = ops.get_marker_mask(self.markers)
+        # global normalisers (src/video_mocap/losses/chamfer_distance.py:20 divides by sum(weights))
+        fg = torch.tensor([float(self.F // groups), float(self.mask.sum().item()) / groups], dtype=torch.float64)
+        fg = self.shard.all_reduce_sum(fg)
+        self.F_global, self.wsum_global = int(fg[0].item()), float(fg[1].item())
+        self.ws = self.mh.workspace(self.F)
+        self.vertices = None
+        self.idx = torch.empty((self.F, self.M), dtype=torch.int32, device=dev)
+        self.d2 = torch.empty((self.F, self.M), dtype=torch.float32, device=dev)
+        self.g_rows = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
+        self.virt = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
+        self.red = torch.zeros(16, dtype=torch.float32, device=dev)       # [d/d betas (<=10) | pad | loss @ 15]
+        self.gbetas_rows = None
+        self.mm = None                                     # per-frame marker mean (trans_vel)
+        self.n_closure = 0
+
+    # -- thin C-ABI call helpers -------------------------------------------------------------
+    def _st(self):
+        return stream_ptr(self.dev)
+
+    def lbs_forward(self, betas_rows, root, pose, yaw, trans):
+        if self.vertices is None:
+            self.vertices = torch.empty((self.F, self.mh.V, 3), dtype=torch.float32, device=self.dev)
+        check(_lib.lib().uuo_lbs_forward(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
+                                         POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(self.vertices), None,
+                                         ptr(self.ws), self._st()))
+        return self.vertices
+
+    def lbs_forward_rows(self, betas_rows, root, pose, yaw, trans, rows, shared):
+        R = rows.shape[-1]
+        check(_lib.lib().uuo_lbs_forward_rows(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
+                                              POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(rows), 1 if shared else 0, R,
+                                              ptr(self.virt), None, ptr(self.ws), self._st()))
+        return self.virt
+
+    def lbs_backward_rows(self, betas_rows, root, pose, yaw, rows, shared, g_rows, g_betas, g_root, g_pose, g_yaw, g_trans):
+        R = rows.shape[-1]
+        check(_lib.lib().uuo_lbs_backward_rows(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
+                                               POSE_RAW6D, ptr(yaw), self.F, ptr(rows), 1 if shared else 0, R,
+                                               ptr(g_rows), None, ptr(self.ws), ptr(g_betas), ptr(g_root), ptr(g_pose),
+                                               ptr(g_yaw), ptr(g_trans), self._st()))
+
+    def sqdiff(self, x, y, scale, g):
+        check(_lib.lib().uuo_sqdiff_accumulate(ptr(x), ptr(y), x.numel(), float(scale), ptr(self.red[15:]), ptr(g),
+                                               self._st()))
+
+    def betas_rows(self, betas):
+        """[G,NB] parameter -> rows handed to the kernels ([1,NB] shared, or [F,NB] for stacked hypotheses)."""
+        if self.groups == 1:
+            return betas.reshape(1, -1)
+        return torch.repeat_interleave(betas.reshape(self.groups, -1), self.F // self.groups, dim=0).contiguous()
+
+    def reduce_gbetas(self, g_betas_param):
+        """d/d betas: (a) stacked hypotheses: per-frame rows -> per-group sums; (b) all-reduce over shards."""
+        if self.groups > 1:
+            g_betas_param.copy_(self.gbetas_rows.view(self.groups, self.F // self.groups, -1).sum(1))
+            return
+        nb = self.mh.NB
+        self.shard.all_reduce_sum_(self.red)               # one 16-float all-reduce: d betas + loss
+        g_betas_param.copy_(self.red[:nb].view_as(g_betas_param))
+
+    def gbetas_target(self):
+        if self.groups == 1:
+            return self.red
+        if self.gbetas_rows is None:
+            self.gbetas_rows = torch.empty((self.F, self.mh.NB), dtype=torch.float32, device=self.dev)
+        return self.gbetas_rows
+
+
+@dataclass
+class ParamBlock:
+    """Flat fp32 parameter / gradient block with named views (one fused Adam launch over all of it)."""
+    flat: torch.Tensor
+    grad: torch.Tensor
+    views: Dict[str, torch.Tensor]
+    gviews: Dict[str, torch.Tensor]
+
+    @classmethod
+    def build(cls, tensors: Dict[str, torch.Tensor], device):
+        n = sum(t.numel() for t in tensors.values())
+        flat = torch.empty(n, dtype=torch.float32, device=device)
+        grad = torch.zeros(n, dtype=torch.float32, device=device)
+        views, gviews, off = {}, {}, 0
+        for k, t in tensors.items():
+            m = t.numel()
+            # keep every view 16-byte aligned?  not required: the kernels only need 4-byte alignment here
+            views[k] = flat[off:off + m].view(t.shape)
+            gviews[k] = grad[off:off + m].view(t.shape)
+            views[k].copy_(t.detach().to(device, torch.float32))
+            off += m
+        return cls(flat, grad, views, gviews)
+
+
+def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor, losses: Dict[str, float]) -> torch.Tensor:
+    """closure_stage_chamfer (optimization.py:187-258): fills pb.grad, returns the loss (device scalar).
+    Parameters: trans [F,3], z_angle [F], betas [G,10], pose_body [F,23,3,3]; root_orient is constant."""
+    v, g = pb.views, pb.gviews
+    F, M, Fg = prob.F, prob.M, prob.F_global
+    pb.grad.zero_()
+    prob.red.zero_()
+    brows = prob.betas_rows(v["betas"])
+    with torch.cuda.device(prob.dev):
+        verts = prob.lbs_forward(brows, root_orient, v["pose_body"], v["z_angle"], v["trans"])
+        w_ch = float(losses.get("full_chamfer", 0.0))
+        if w_ch != 0.0 and prob.wsum_global > 0:
+            check(_lib.lib().uuo_nn_argmin(ptr(prob.markers), ptr(verts), F, M, prob.mh.V, ptr(prob.d2), ptr(prob.idx),
+                                           prob._st()))
+            check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.idx), F, M,
+                                              prob.mh.V, w_ch / prob.wsum_global, ptr(prob.red[15:]), ptr(prob.g_rows),
+                                              prob._st()))
+        else:
+            prob.g_rows.zero_()
+            prob.idx.zero_()
+        prob.lbs_backward_rows(brows, root_orient, v["pose_body"], v["z_angle"], prob.idx, False, prob.g_rows,
+                               prob.gbetas_target(), None, g["pose_body"], g["z_angle"], g["trans"])
+        if "reg_pose_body" in losses:                                                   # :243-245
+            prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
+                        g["pose_body"])
+        if "trans_vel" in losses:                                                       # :246-250
+            if prob.groups > 1:
+                raise ValueError("trans_vel is not defined across stacked hypotheses")
+            if prob.mm is None:
+                prob.mm = torch.empty((F, 3), dtype=torch.float32, device=prob.dev)
+                check(_lib.lib().uuo_marker_mean(ptr(prob.markers), F, M, ptr(prob.mm), prob._st()))
+            halo_src = torch.cat([v["trans"], prob.mm], dim=1)                          # [F,6]
+            prev, nxt = exchange_halo(halo_src, 1, prob.shard)
+            check(_lib.lib().uuo_transvel_accumulate(ptr(v["trans"]), ptr(prob.mm), ptr(prev), ptr(nxt), F,
+                                                     losses["trans_vel"] / ((Fg - 1) * 3), ptr(prob.red[15:]),
+                                                     ptr(g["trans"]), prob._st()))
+        prob.reduce_gbetas(g["betas"])
+        if prob.groups > 1:
+            prob.shard.all_reduce_sum_(prob.red)
+        if "reg_betas" in losses:                                                       # :255-256 (same on every rank)
+            ob = prob.o_betas.expand_as(v["betas"]).contiguous()
+            prob.sqdiff(v["betas"], ob, losses["reg_betas"] / v["betas"][0].numel(), g["betas"])
+    prob.n_closure += 1
+    return prob.red[15]
+
+
+def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, losses: Dict[str, float]) -> torch.Tensor:
+    """closure_stage_marker_pose (optimization.py:329-377).  Parameters: pose_body, betas, root_orient, trans."""
+    v, g = pb.views, pb.gviews
+    F, M, Fg = prob.F, prob.M, prob.F_global
+    pb.grad.zero_()
+    prob.red.zero_()
+    brows = prob.betas_rows(v["betas"])
+    with torch.cuda.device(prob.dev):
+        virt = prob.lbs_forward_rows(brows, v["root_orient"], v["pose_body"], None, v["trans"], vertex_idx, True)
+        if "marker" in losses:                                                          # :356-362 (mean over ALL F*M)
+            check(_lib.lib().uuo_marker_loss_rows(ptr(prob.markers), ptr(virt), ptr(prob.mask), F * M, MARKER_DISTANCE,
+                                                  losses["marker"] / (Fg * M), ptr(prob.red[15:]), ptr(prob.g_rows),
+                                                  prob._st()))
+        else:
+            prob.g_rows.zero_()
+        prob.lbs_backward_rows(brows, v["root_orient"], v["pose_body"], None, vertex_idx, True, prob.g_rows,
+                               prob.gbetas_target(), g["root_orient"], g["pose_body"], None, g["trans"])
+        if "reg_pose_body" in losses:                                                   # :363-365
+            prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
+                        g["pose_body"])
+        if "temporal" in losses:                                                        # :368-374
+            if prob.groups > 1:
+                raise ValueError("the temporal term is not defined across stacked hypotheses")
+            D = v["pose_body"][0].numel()
+            x = v["pose_body"].view(F, D)
+            prev, nxt = exchange_halo(x, 2, prob.shard)
+            check(_lib.lib().uuo_temporal_accumulate(ptr(x), ptr(prev), ptr(nxt), F, D,
+                                                     losses["temporal"] / ((Fg - 2) * D), ptr(prob.red[15:]),
+                                                     ptr(g["pose_body"]), prob._st()))
+        prob.reduce_gbetas(g["betas"])
+        if prob.groups > 1:
+            prob.shard.all_reduce_sum_(prob.red)
+        if "reg_betas" in losses:                                                       # :366-367
+            ob = prob.o_betas.expand_as(v["betas"]).contiguous()
+            prob.sqdiff(v["betas"], ob, losses["reg_betas"] / v["betas"][0].numel(), g["betas"])
+    prob.n_closure += 1
+    return prob.red[15]
+
+
+# ------------------------------------------------------------------------------------------------
+# optimiser drivers
+# ------------------------------------------------------------------------------------------------
+def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int, lr: float,
+             betas=(0.9, 0.999), eps: float = 1e-8, on_iter: Optional[Callable] = None) -> Optional[torch.Tensor]:
+    """closure -> fused Adam over the flat block.  No host synchronisation inside the loop unless
+    ``on_iter`` asks for the loss."""
+    m = torch.zeros_like(pb.flat)
+    v = torch.zeros_like(pb.flat)
+    loss = None
+    for it in range(1, num_iters + 1):
+        loss = closure()
+        ops.adam_step(pb.flat, pb.grad, m, v, lr, it, betas, eps)
+        if on_iter is not None:
+            on_iter(it - 1, loss)
+    return loss
+
+
+def run_lbfgs(pb: ParamBlock, closure: Callable[[], torch.Tensor], max_iter: int, lr: float,
+              tolerance_grad: float = 1e-7, tolerance_change: float = 1e-9) -> int:
+    """The reference's optimiser call (optimization.py:176-183,279) around the CUDA closure."""
+    p = pb.flat.requires_grad_(True)
+    opt = torch.optim.LBFGS([p], max_iter=max_iter, tolerance_grad=tolerance_grad, tolerance_change=tolerance_change,
+                            lr=lr, line_search_fn="strong_wolfe")
+    n = [0]
+
+    def cl():
+        with torch.no_grad():
+            loss = closure()
+        p.grad = pb.grad
+        n[0] += 1
+        return loss.clone()
+
+    opt.step(cl)
+    pb.flat.requires_grad_(False)
+    return n[0]
+
+
+def _optimise(pb, closure, stage_cfg, opt_cfg, lbfgs_lr, on_iter=None):
+    name = str(opt_cfg.get("name", "adam")).lower()
+    iters = int(stage_cfg["num_iters"])
+    if iters <= 0:
+        return
+    if name == "adam":
+        run_adam(pb, closure, iters, float(stage_cfg.get("lr_adam", opt_cfg.get("lr", 0.01))), on_iter=on_iter)
+    elif name == "lbfgs":
+        run_lbfgs(pb, closure, iters, lbfgs_lr, float(opt_cfg.get("tolerance_grad", 1e-7)),
+                  float(opt_cfg.get("tolerance_change", 1e-9)))
+    else:
+        raise ValueError("optimizer.name must be 'adam' or 'lbfgs'")
+
+
+# ------------------------------------------------------------------------------------------------
+# the reference's stage functions
+# ------------------------------------------------------------------------------------------------
+def get_marker_mask(markers: torch.Tensor) -> torch.Tensor:
+    """optimization.py:703-715."""
+    return ops.get_marker_mask(markers) != 0
+
+
+def weighted_chamfer_distance(x: torch.Tensor, y: torch.Tensor, x_weights: torch.Tensor,
+                              single_directional: bool = False, return_idx: bool = False):
+    """src/video_mocap/losses/chamfer_distance.py:5-21 (always single-directional there): value only, no
+    [F*M,V,3] intermediate.  x markers [F,M,3], y vertices [F,V,3], x_weights [F,M]."""
+    d, idx = ops.nn_argmin(x, y)
+    w = x_weights.to(d.dtype).reshape(-1)
+    s = w.sum()
+    val = (d.reshape(-1) * w).sum() / s if float(s) != 0.0 else d.sum() * 0.0
+    return (val, idx) if return_idx else (val, None)
+
+
+def rot_z(angle: torch.Tensor) -> torch.Tensor:
+    """compute_root_orient_z (optimization.py:672-679): [...,1] -> [...,3,3]."""
+    c, s = torch.cos(angle[..., 0]), torch.sin(angle[..., 0])
+    z, o = torch.zeros_like(c), torch.ones_like(c)
+    return torch.stack([c, -s, z, s, c, z, z, z, o], dim=-1).reshape(angle.shape[:-1] + (3, 3))
+
+
+def normalize_rot(m: torch.Tensor) -> torch.Tensor:
+    """multimodal.py:34-35 (6D round trip) for the final packing step -- small torch ops on the device."""
+    a1, a2 = m[..., 0, :], m[..., 1, :]
+    b1 = torch.nn.functional.normalize(a1, dim=-1)
+    b2 = torch.nn.functional.normalize(a2 - (b1 * a2).sum(-1, keepdim=True) * b1, dim=-1)
+    return torch.stack((b1, b2, torch.cross(b1, b2, dim=-1)), dim=-2)
+
+
+def optim_chamfer(markers, pose_body, o_pose_body, betas, o_betas, root_orient, trans, img_mask, marker_labels,
+                  smpl_inference, config: Dict, initial_angle: float = 0, repeat: int = 0, verbose: bool = False,
+                  iter_fn: Callable = None, shard: Optional[Shard] = None, groups: int = 1, problem=None):
+    """optimization.py:147-285.  Updates trans, betas, pose_body and root_orient IN PLACE like the reference
+    (its parameters are leaf tensors stepped by the optimiser; root_orient gets the fitted yaw baked in)."""
+    st = config["stages"]["chamfer"]
+    if not st.get("yaw_lock", True):
+        raise NotImplementedError("yaw_lock: False (free 3x3 root offset) is not on the CUDA path")
+    prob = problem or FitProblem(smpl_inference, markers, o_pose_body, o_betas, shard, groups)
+    F = prob.F
+    dev = prob.dev
+    root = root_orient.detach().to(dev, torch.float32).contiguous()
+    pb = ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F, device=dev), "betas": betas.reshape(-1, prob.mh.NB),
+                           "pose_body": pose_body}, dev)
+    losses = dict(st["losses"])
+    closure = lambda: chamfer_closure(prob, pb, root, losses)
+    cb = None
+    if verbose or iter_fn is not None:
+        def cb(it, loss):
+            if verbose:
+                print("Chamfer", it, float(loss))
+    _optimise(pb, closure, st, config.get("optimizer", {}), 0.1, cb)
+    with torch.no_grad():
+        trans.copy_(pb.views["trans"])
+        betas.copy_(pb.views["betas"].view_as(betas))
+        pose_body.copy_(pb.views["pose_body"])
+        root_orient.copy_(rot_z(pb.views["z_angle"].view(F, 1, 1)) @ root)          # :280-285
+    return prob
+
+
+def optim_markers(markers, pose_body, o_pose_body, betas, o_betas, root_orient, trans, barycentric_coords_one_hot,
+                  img_mask, smpl_inference, config: Dict, initial_angle: float = 0, repeat: int = 0,
+                  verbose: bool = False, iter_fn: Callable = None, shard: Optional[Shard] = None, groups: int = 1,
+                  problem=None):
+    """optimization.py:288-399.  ``barycentric_coords_one_hot`` is the reference's [M,V] one-hot matrix or the
+    equivalent vertex-index vector [M]."""
+    st = config["stages"]["marker"]
+    if st.get("use_sdf", False):
+        raise NotImplementedError("use_sdf needs the reference's SDF checkpoints (not shipped)")
+    prob = problem or FitProblem(smpl_inference, markers, o_pose_body, o_betas, shard, groups)
+    dev = prob.dev
+    vidx = barycentric_coords_one_hot
+    if vidx.dim() == 2:
+        vidx = torch.argmax(vidx, dim=1)
+    vidx = vidx.to(dev, torch.int32).contiguous()
+    pb = ParamBlock.build({"pose_body": pose_body, "betas": betas.reshape(-1, prob.mh.NB), "root_orient": root_orient,
+                           "trans": trans}, dev)
+    losses = dict(st["losses"])
+    closure = lambda: marker_closure(prob, pb, vidx, losses)
+    cb = None
+    if verbose:
+        cb = lambda it, loss: print("Marker", it, float(loss))
+    _optimise(pb, closure, st, config.get("optimizer", {}), 1.0, cb)
+    with torch.no_grad():
+        pose_body.copy_(pb.views["pose_body"])
+        betas.copy_(pb.views["betas"].view_as(betas))
+        root_orient.copy_(pb.views["root_orient"])
+        trans.copy_(pb.views["trans"])
+    return prob
+
+
+def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_inference, marker_labels=None,
+                           granularity: str = "full", img_mask=None, device=None, config: Optional[Dict] = None,
+                           o_pose_body=None, window_size: int = 1, use_velocity: bool = True,
+                           shard: Optional[Shard] = None, as_one_hot: bool = True):
+    """optimization.py:402-642, the shipped ``use_mean: True`` branch (:422-430,464-486,595-603): SMPL forward
+    with the mean betas, mean over the frames with img_mask == 1 of the marker-vertex distances, argmin.
+    Returns the [M,V] one-hot matrix like the reference (or the index vector)."""
+    if config is not None:
+        cl = config["stages"].get("compute_locations", {})
+        if not cl.get("use_mean", True) or cl.get("use_barycentric", False):
+            raise NotImplementedError("only compute_locations.use_mean (the shipped setting) is on the CUDA path")
+    smpl = _model_of(smpl_inference)
+    mh = smpl.handle
+    dev = mh.device
+    shard = shard or Shard()
+    mk = markers.to(dev, torch.float32).contiguous()
+    F, M = mk.shape[:2]
+    mean_betas = torch.mean(betas.to(dev, torch.float32).reshape(-1, mh.NB), dim=0, keepdim=True).contiguous()   # :424
+    vertices = torch.empty((F, mh.V, 3), dtype=torch.float32, device=dev)
+    ws = mh.workspace(F)
+    pose = pose_body.detach().to(dev, torch.float32).contiguous()
+    root = root_orient.detach().to(dev, torch.float32).contiguous()
+    tr = trans.detach().to(dev, torch.float32).contiguous()
+    with torch.cuda.device(dev):
+        check(_lib.lib().uuo_lbs_forward(mh.handle, ptr(mean_betas), 1, ptr(root), ptr(pose), POSE_RAW6D, None, ptr(tr), F,
+                                         ptr(vertices), None, ptr(ws), stream_ptr(dev)))
+    fm = img_mask.to(dev, torch.float32).contiguous() if img_mask is not None else None
+    _, acc = ops.mean_distance_argmin(mk, vertices, fm, finalize=False)
+    cnt = torch.tensor([float(F if fm is None else (fm == 1).sum().item())], dtype=torch.float64)
+    cnt = shard.all_reduce_sum(cnt)
+    shard.all_reduce_sum_(acc)                                                       # [M,V] fp32, once per stage
+    idx = ops.mean_argmin(acc, max(float(cnt.item()), 1.0))
+    if not as_one_hot:
+        return idx
+    one_hot = torch.zeros((M, mh.V), dtype=torch.float32, device=dev)                # :601-603
+    one_hot[torch.arange(M, device=dev), idx.long()] = 1.0
+    return one_hot
+
+
+def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient, trans, img_mask, smpl_inference,
+                   config: Dict, angles, shard: Optional[Shard] = None):
+    """The MHT loop of multimodal.py:462-606 batched: every yaw hypothesis becomes a block of frames of ONE
+    stacked problem (chamfer stage -> correspondences -> marker stage), scored by the weighted chamfer
+    distance (:576-599).  Returns (best index, per-hypothesis scores, list of fitted parameter dicts)."""
+    smpl = _model_of(smpl_inference)
+    dev = smpl.handle.device
+    H = len(angles)
+    F = markers.shape[0]
+    T = lambda t: t.detach().to(dev, torch.float32)
+    rep = lambda t: T(t).repeat((H,) + (1,) * (t.dim() - 1)).contiguous()
+    mk, opose = rep(markers), rep(o_pose_body)
+    pose, tr = rep(pose_body), rep(trans)
+    ang = torch.as_tensor(list(angles), dtype=torch.float32, device=dev)
+    root = (rot_z(ang.view(H, 1, 1, 1)) @ T(root_orient).unsqueeze(0)).reshape(H * F, 1, 3, 3).contiguous()   # :465
+    bet = T(betas).reshape(1, -1).repeat(H, 1).contiguous()
+    obet = T(o_betas).reshape(1, -1)
+    prob = FitProblem(smpl, mk, opose, obet, shard, groups=H)
+    optim_chamfer(mk, pose, opose, bet, obet, root, tr, None, None, smpl, config, problem=prob, groups=H)
+    # correspondences per hypothesis (they do not mix frames of different hypotheses)
+    vidx = []
+    for h in range(H):
+        sl = slice(h * F, (h + 1) * F)
+        vidx.append(compute_nearest_points(mk[sl], pose[sl], bet[h:h + 1], root[sl], tr[sl], smpl, img_mask=img_mask,
+                                           config=config, shard=shard, as_one_hot=False))
+    scores, fitted = [], []
+    for h in range(H):
+        sl = slice(h * F, (h + 1) * F)
+        p = {"pose_body": pose[sl].clone(), "betas": bet[h:h + 1].clone(), "root_orient": root[sl].clone(),
+             "trans": tr[sl].clone()}
+        optim_markers(mk[sl], p["pose_body"], opose[sl], p["betas"], obet, p["root_orient"], p["trans"], vidx[h],
+                      img_mask, smpl, config, shard=shard)
+        out = smpl(betas=p["betas"], body_pose=normalize_rot(p["pose_body"]), global_orient=normalize_rot(p["root_orient"]),
+                   transl=p["trans"], pose2rot=False)
+        val, _ = weighted_chamfer_distance(mk[sl], out.vertices, ops.get_marker_mask(mk[sl]))
+        tot = torch.stack([val * float(ops.get_marker_mask(mk[sl]).sum()), ops.get_marker_mask(mk[sl]).sum()]).double().cpu()
+        tot = (shard or Shard()).all_reduce_sum(tot)
+        scores.append(float(tot[0] / tot[1]) if float(tot[1]) > 0 else 0.0)
+        p["vertex_idx"] = vidx[h]
+        fitted.append(p)
+    best = int(np.argmin(scores))
+    return best, scores, fitted
+
+
+def load_config(filename: str) -> Dict:
+    """src/video_mocap/utils/config.py:6-18: YAML whose ``parent:`` names another config file (a path, as in
+    config/mht_rotation.yaml:2), loaded recursively and deep-merged with mergedeep.merge({}, parent, child)
+    semantics (mergedeep is not installed here, hence the 6-line merge)."""
+    import os
+    import yaml
+
+    def merge(a, b):
+        out = dict(a)
+        for k, v in b.items():
+            out[k] = merge(out[k], v) if isinstance(v, dict) and isinstance(out.get(k), dict) else v
+        return out
+
+    with open(filename, "r") as stream:
+        output = yaml.safe_load(stream)
+    parent = output.get("parent")
+    if parent is not None:
+        if not os.path.exists(parent):       # the reference resolves it against the working directory
+            alt = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(filename))), parent)
+            parent = alt if os.path.exists(alt) else parent
+        output = merge(load_config(parent), output)
+    return output
+
+
+def default_config(num_iters: int = 200, optimizer: str = "adam", lr: float = 0.01) -> Dict:
+    """The schema and loss weights of config/video_mocap.yaml:1-58 as a dict (stages that are disabled
+    there, or are outside the hot path, are left out), with the optimiser switchable between the
+    north-star fused Adam and the reference's L-BFGS."""
+    return {
+        "name": "video_mocap", "parent": None, "stage_repeats": 1, "recompute_marker_labels": False,
+        "find_best_part_fits": True, "num_root_orient_angles": 4,
+        "optimizer": {"tolerance_grad": 1.0e-7, "tolerance_change": 1.0e-9, "name": optimizer, "lr": lr},
+        "stages": {
+            "chamfer": {"num_iters": num_iters, "losses": {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0},
+                        "single_directional": True, "yaw_lock": True},
+            "compute_locations": {"use_velocity": False, "use_barycentric": False, "use_mean": True},
+            "marker": {"num_iters": num_iters, "losses": {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0},
+                       "use_sdf": False},
+        },
+    }
