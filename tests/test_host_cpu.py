@@ -1,0 +1,141 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/uuo_mocap.h declares (no compute
+calls), config loading, frame-range sharding and the halo exchange (gloo, world_size 2)."""
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from uuo_mocap_b200 import _lib, build
+    build.build_lib()
+    hdr = open(os.path.join(ROOT, "include", "uuo_mocap.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(uuo_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    l = _lib.lib()
+    for name in declared:
+        assert getattr(l, name) is not None
+    assert l.uuo_version() >= 100
+    assert l.uuo_last_error() is not None
+
+
+def test_no_cpu_fallback():
+    """The product path refuses CPU devices / tensors instead of silently computing elsewhere."""
+    from uuo_mocap_b200 import _lib, ops, synthetic
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    with pytest.raises(_lib.UuoError):
+        SMPL(_as_struct(synthetic.make_model("top4")), device="cpu")
+    with pytest.raises(_lib.UuoError):
+        ops.nn_argmin(torch.zeros(1, 2, 3), torch.zeros(1, 5, 3))
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "uuo-mocap_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), fn
+
+
+def test_load_config_parent_merge(tmp_path):
+    from uuo_mocap_b200.fit import load_config, default_config
+    (tmp_path / "config").mkdir()
+    base = tmp_path / "config" / "base.yaml"
+    base.write_text("name: base\nparent:\nnum_root_orient_angles: 4\nstages:\n  chamfer:\n    num_iters: 10\n    losses:\n      full_chamfer: 10.0\n")
+    child = tmp_path / "config" / "child.yaml"
+    child.write_text("name: child\nparent: %s\nnum_root_orient_angles: 1\nstages:\n  chamfer:\n    num_iters: 3\n" % base)
+    cfg = load_config(str(child))
+    assert cfg["name"] == "child" and cfg["num_root_orient_angles"] == 1
+    assert cfg["stages"]["chamfer"] == {"num_iters": 3, "losses": {"full_chamfer": 10.0}}
+    d = default_config()
+    assert d["stages"]["chamfer"]["losses"] == {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0}
+    assert d["stages"]["marker"]["losses"] == {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0}
+
+
+def test_frame_range_partitions():
+    from uuo_mocap_b200.dist import frame_range
+    for F in (1, 7, 300, 100000):
+        for w in (1, 2, 4, 8):
+            r = [frame_range(F, k, w) for k in range(w)]
+            assert r[0][0] == 0 and r[-1][1] == F
+            assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+            sizes = [b - a for a, b in r]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _temporal_ref(x):
+    """optimization.py:368-374 as written."""
+    x = x.clone().requires_grad_(True)
+    vel = x[2:] - 2 * x[1:-1] - x[:-2]
+    loss = torch.nn.functional.mse_loss(vel, torch.zeros_like(vel))
+    loss.backward()
+    return loss.detach(), x.grad
+
+
+def _temporal_shard(x, prev, nxt, F_global):
+    """What uuo_temporal_accumulate computes for one shard, restated with torch for the gloo test."""
+    rows = [t for t in (prev, x, nxt) if t is not None]
+    off = 0 if prev is None else prev.shape[0]
+    full = torch.cat(rows, 0).clone().requires_grad_(True)
+    D = x.shape[1]
+    F = x.shape[0]
+    e = full[2:] - 2 * full[1:-1] - full[:-2]                     # e_t for t = -off .. ; own terms: t in [0,F)
+    t_idx = torch.arange(e.shape[0]) - off
+    own = (t_idx >= 0) & (t_idx < F)
+    scale = 1.0 / ((F_global - 2) * D)
+    # gradient of ALL terms touching own rows, loss of own terms only
+    (scale * (e ** 2).sum()).backward()
+    return scale * (e[own] ** 2).sum().detach(), full.grad[off:off + F]
+
+
+def _worker(rank, world, port, F, D, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, ROOT)
+    import uuo_mocap_b200  # noqa: F401
+    from uuo_mocap_b200.dist import Shard, exchange_halo
+    torch.manual_seed(0)
+    x_all = torch.randn(F, D)
+    sh = Shard.from_env()
+    a, b = sh.range(F)
+    x = x_all[a:b].contiguous()
+    prev, nxt = exchange_halo(x, 2, sh)
+    if rank > 0:
+        assert torch.equal(prev, x_all[a - 2:a])
+    else:
+        assert prev is None
+    if rank < world - 1:
+        assert torch.equal(nxt, x_all[b:b + 2])
+    else:
+        assert nxt is None
+    loss, g = _temporal_shard(x, prev, nxt, F)
+    red = torch.zeros(16)
+    red[15] = loss
+    red[:3] = float(rank + 1)
+    sh.all_reduce_sum_(red)
+    cnt = sh.all_reduce_sum(torch.tensor([float(b - a)], dtype=torch.float64))
+    ref_loss, ref_g = _temporal_ref(x_all)
+    ok = (abs(float(red[15]) - float(ref_loss)) < 1e-6 * abs(float(ref_loss)) and
+          torch.allclose(g, ref_g[a:b], rtol=1e-5, atol=1e-7) and int(cnt.item()) == F and
+          float(red[0]) == sum(range(1, world + 1)))
+    out[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2])
+def test_halo_exchange_and_sharded_temporal_gloo(world):
+    mgr = mp.Manager()
+    out = mgr.dict()
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(world, port, 11, 5, out), nprocs=world, join=True)
+    assert all(out.get(r) for r in range(world)), dict(out)
