@@ -37,9 +37,10 @@ extern "C" int uuo_lbs_backward(const uuo_model* m, const float* betas, int beta
   cudaStream_t st = (cudaStream_t)stream;
   uuo_ws ws = carve_ws(m, F, workspace);
   if ((rc = launch_skin_backward(m, F, g_vertices, g_joints, ws, st))) return rc;
-  if ((rc = launch_gcoef_gemm(m, F, ws, st))) return rc;
+  int n_gc = 0;
+  if ((rc = launch_gcoef_gemm(m, F, ws, &n_gc, st))) return rc;
   return launch_fk_backward(m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, F, g_joints, ws,
-                            UUO_NSPLIT_GA, UUO_NSPLIT_GC, nullptr, g_betas, g_global_orient, g_body_pose, g_yaw,
+                            UUO_NSPLIT_GA, n_gc, nullptr, g_betas, g_global_orient, g_body_pose, g_yaw,
                             g_transl, st);
 }
 

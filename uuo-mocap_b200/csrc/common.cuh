@@ -6,13 +6,15 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/uuo_mocap.h"
 
 #define UUO_MAX_J 32       // one lane per joint in the FK kernels
 #define UUO_MAX_CHILD 4    // children per joint handled by the reverse tree sweep
 #define UUO_SKIN_J 24      // the dense skinning kernels are compiled for the SMPL joint count
 #define UUO_NSPLIT_GA 4    // vertex splits of the skinning-backward dA reduction (deterministic partials)
-#define UUO_NSPLIT_GC 8    // K splits of the posedirs-transpose GEMM (deterministic partials)
+#define UUO_NSPLIT_GC 16   // K splits of the posedirs-transpose GEMM (deterministic partials)
 #define UUO_GA_STRIDE 292  // 288 dA entries + 3 (sum_v g_v) + 1 pad
 
 struct uuo_model {
@@ -33,6 +35,8 @@ struct uuo_model {
   float* ell_w;   // [V][4]
   int32_t* extra_ids;  // [NE]
   uint8_t* vflag;      // [V] 1 when some extra joint is this vertex
+  float* Bimg_fwd;     // [NP/256][KP/32][2][256*32] tf32 hi|lo SWIZZLE_128B tiles of Bt   (umma_gemm.cu)
+  float* Bimg_bwd;     // [1][NP/32][2][KP*32]       tf32 hi|lo SWIZZLE_128B tiles of Bmat
   // small tables passed by value to the FK kernels
   int8_t parents[UUO_MAX_J];
   int8_t depth[UUO_MAX_J];
@@ -137,8 +141,13 @@ int launch_fk_backward(const uuo_model* m, const float* betas, int betas_rows, c
                        int pose_mode, const float* yaw, int F, const float* g_joints, const uuo_ws& ws,
                        int n_ga_parts, int n_gc_parts, const float* g_rows_sum /*unused*/,
                        float* g_betas, float* g_go, float* g_bp, float* g_yaw, float* g_transl, cudaStream_t st);
+// host: rows x K fp32 (K contiguous, pitch ld = K) -> [rows/NT][K/32][2][NT*32] swizzled tf32 hi|lo tiles
+void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int K, int NT);
 int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
-int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st);
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+int uuo_gcoef_splits(const uuo_model* m, int F);
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st);
 int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, const float* g_joints,

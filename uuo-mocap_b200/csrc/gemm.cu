@@ -3,6 +3,8 @@
 //            (lbs.py:209 blend_shapes + lbs.py:229-233 posedirs matmul, one GEMM of K = P + NB)
 //   backward g_coef[F,KP]  = g_vposed[F,NP] @ Bt[NP,KP]   (split-K, deterministic partials)
 // Register-tiled 16x16 threads, TM x TN outputs per thread, BK = 8, register-prefetched double buffer.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 template <int TM, int TN>
@@ -123,7 +125,14 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ Am
   }
 }
 
+// UUO_GEMM_SIMT=1 selects the exact-fp32 SIMT kernels above (debug cross-check of the tensor-core path)
+static bool use_simt() {
+  const char* e = getenv("UUO_GEMM_SIMT");   // read per call so one process can compare both paths
+  return e && e[0] == '1';
+}
+
 int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+  if (!use_simt()) return launch_vposed_gemm_umma(m, F, ws, st);
   // M = F, K = KP, N = NP (padded columns are zeros in Bmat and vt)
   dim3 grid(m->NP / 128, (F + 127) / 128, 1);
   { ProfScope ps_("vposed_gemm", st);
@@ -133,10 +142,14 @@ int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t
   return UUO_OK;
 }
 
-int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
-  // M = F, K = NP split in UUO_NSPLIT_GC chunks, N = KP
-  const int kchunk = m->NP / UUO_NSPLIT_GC;   // NP is a multiple of 128 -> chunk multiple of 16
-  dim3 grid((m->KP + 111) / 112, (F + 127) / 128, UUO_NSPLIT_GC);
+// returns the number of partial slabs written to ws.gcoef through *n_parts
+int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st) {
+  if (!use_simt()) { *n_parts = uuo_gcoef_splits(m, F); return launch_gcoef_gemm_umma(m, F, ws, st); }
+  // M = F, K = NP split in 8 chunks, N = KP
+  const int nsplit = 8;
+  *n_parts = nsplit;
+  const int kchunk = m->NP / nsplit;   // NP is a multiple of 256 -> chunk multiple of 32
+  dim3 grid((m->KP + 111) / 112, (F + 127) / 128, nsplit);
   { ProfScope ps_("gcoef_gemm", st);
   sgemm_kernel<8, 7><<<grid, 256, 0, st>>>(ws.gvposed, m->NP, F, m->Bt, m->KP, kchunk, ws.gcoef, m->KP, m->KP,
                                            nullptr, (size_t)F * m->KP);

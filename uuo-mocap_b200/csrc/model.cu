@@ -53,8 +53,8 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   memset(m, 0, sizeof(*m));
   m->V = V; m->J = J; m->NB = NB; m->P = P; m->NE = NE; m->device = device;
   m->KC = P + NB;
-  m->KP = (m->KC + 15) / 16 * 16;
-  m->NP = (3 * V + 127) / 128 * 128;
+  m->KP = (m->KC + 31) / 32 * 32;      // K blocks of the tensor-core GEMMs are 32 fp32 (one 128 B swizzle row)
+  m->NP = (3 * V + 255) / 256 * 256;   // forward GEMM column tiles are 256 wide
   const int KP = m->KP, NP = m->NP, N = 3 * V;
 
   // kinematic tree tables
@@ -115,6 +115,13 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
     }
     m->max_nnz = std::max(m->max_nnz, nnz);
   }
+  // tensor-core operand images (umma_gemm.cu): forward B rows = vertex coordinates (K = KP),
+  // backward B rows = coefficients (K = NP); both pre-split into tf32 hi | lo and pre-swizzled.
+  std::vector<float> img_fwd, img_bwd;
+  uuo_build_b_image(img_fwd, Bt.data(), NP, KP, 256);
+  uuo_build_b_image(img_bwd, Bmat.data(), KP, NP, KP);
+  UUO_CHECK_ARG(KP <= 256 && KP % 16 == 0, "KP must be <= 256");
+
   std::vector<uint8_t> vflag(V, 0);
   std::vector<int32_t> ex(std::max(NE, 1), 0);
   for (int e = 0; e < NE; ++e) { ex[e] = extra_joint_ids[e]; vflag[ex[e]] = 1; }
@@ -123,7 +130,8 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   if ((rc = upload(&m->vt, vt)) || (rc = upload(&m->Bmat, Bmat)) || (rc = upload(&m->Bt, Bt)) ||
       (rc = upload(&m->J0, J0)) || (rc = upload(&m->Jdirs, Jdirs)) || (rc = upload(&m->W, W)) ||
       (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
-      (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag))) {
+      (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag)) ||
+      (rc = upload(&m->Bimg_fwd, img_fwd)) || (rc = upload(&m->Bimg_bwd, img_bwd))) {
     uuo_model_destroy(m);
     return rc;
   }
@@ -135,6 +143,7 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
   if (!m) return;
   cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
   cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
+  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd);
   delete m;
 }
 

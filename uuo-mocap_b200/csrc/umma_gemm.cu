@@ -1,0 +1,313 @@
+// The two dense contractions of lbs() on the 5th-gen tensor cores (tcgen05.mma kind::tf32, TMEM accumulators),
+// 3xTF32 split so the result stays at fp32 accuracy (vertices 1e-5 / gradients 1e-4 contract):
+//     x = hi + lo,  hi = tf32(x), lo = tf32(x - hi);   A.B ~= Ahi.Bhi + Alo.Bhi + Ahi.Blo
+//   forward  v_posed[F,NP] = v_template + coef[F,KP] . Bmat[KP,NP]        (lbs.py:209 + lbs.py:229-233)
+//   backward g_coef[F,KP]  = g_vposed[F,NP] . Bmat[KP,NP]^T  (split-K, deterministic partial slabs)
+// Both are C[M,N] = A[M,K] . B[N,K]^T with K-major operands.
+//   * B is a model constant: uuo_model_create stores it pre-split (hi|lo) and pre-swizzled, tile by tile, exactly as
+//     the shared-memory image the MMA descriptor expects, so one 1-D bulk copy (UBLKCP) per stage fetches it.
+//   * A changes every call: 8 producer warps read the fp32 rows (coalesced 128 B), split them and store the
+//     SWIZZLE_128B image of the hi and lo tiles.
+//   * one thread issues the MMAs; accumulators are double buffered in TMEM (2 x 256 columns) so the epilogue of
+//     tile i (tcgen05.ld -> smem transpose -> coalesced stores, + v_template) overlaps the MMAs of tile i+1.
+// Persistent: one CTA per SM walks work items (n_tile, k_split, m_tile) round robin.
+#include <algorithm>
+
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace {
+
+constexpr int BM = 128;             // rows of A per tile (frames)
+constexpr int BK = 32;              // fp32 elements per K block = one 128 B swizzle row
+constexpr int NT_MAX = 256;         // max columns per tile
+constexpr int STAGES = 2;
+constexpr int A_TILE_BYTES = BM * BK * 4;            // 16 KB (hi) + 16 KB (lo)
+constexpr int B_TILE_BYTES_MAX = NT_MAX * BK * 4;    // 32 KB (hi) + 32 KB (lo)
+constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES_MAX;   // 96 KB
+constexpr int EPI_WARPS = 4, PROD_WARPS = 8;
+constexpr int WARP_MMA = EPI_WARPS, WARP_BLOAD = EPI_WARPS + 1, WARP_PROD0 = EPI_WARPS + 2;
+constexpr int NTHREADS = (EPI_WARPS + 2 + PROD_WARPS) * 32;   // 448
+constexpr int STAGING_FLOATS = 32 * 33;              // per epilogue warp, padded transpose tile
+constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + EPI_WARPS * STAGING_FLOATS * 4 + 256;
+
+struct GemmArgs {
+  const float* A; long lda; int M;   // fp32 row-major, K contiguous
+  const float* Bimg;                 // [n_tiles][kb_total][2][NT*32] swizzled images
+  float* C; long ldc; long split_stride;
+  const float* bias;                 // [n_tiles*NT] or null
+  int NT, n_tiles, m_tiles, kb_total, k_splits, kb_per_split, n_valid;
+};
+
+__device__ __forceinline__ void decode_item(const GemmArgs& g, int w, int& mt, int& nt, int& ks) {
+  mt = w % g.m_tiles;
+  int r = w / g.m_tiles;
+  ks = r % g.k_splits;
+  nt = r / g.k_splits;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = umma::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (base - raw);
+  float* staging = reinterpret_cast<float*>(sm + STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + EPI_WARPS * STAGING_FLOATS * 4);
+  // bars: [0,S) full_a, [S,2S) full_b, [2S,3S) empty, [3S,3S+2) tmem_full, [3S+2,3S+4) tmem_empty
+  const uint32_t bar0 = umma::smem_u32(bars);
+  auto FULL_A = [&](int s) { return bar0 + 8u * s; };
+  auto FULL_B = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto EMPTY = [&](int s) { return bar0 + 8u * (2 * STAGES + s); };
+  auto TFULL = [&](int a) { return bar0 + 8u * (3 * STAGES + a); };
+  auto TEMPTY = [&](int a) { return bar0 + 8u * (3 * STAGES + 2 + a); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_items = g.m_tiles * g.n_tiles * g.k_splits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      umma::mbar_init(FULL_A(s), PROD_WARPS);
+      umma::mbar_init(FULL_B(s), 1);
+      umma::mbar_init(EMPTY(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      umma::mbar_init(TFULL(a), 1);
+      umma::mbar_init(TEMPTY(a), EPI_WARPS);
+    }
+    umma::fence_barrier_init();
+  }
+  if (warp == WARP_MMA) umma::tmem_alloc(umma::smem_u32(tmem_slot), 512);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t b_tile_bytes = (uint32_t)g.NT * BK * 4;
+
+  if (warp >= WARP_PROD0) {
+    // ===== A producers: fp32 rows -> (hi, lo) SWIZZLE_128B images =====
+    const int tp = threadIdx.x - WARP_PROD0 * 32;
+    int w = blockIdx.x, mt = 0, nt = 0, ks = 0, kb = 0, kb_end = 0;
+    bool live = w < n_items;
+    if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
+    auto gload = [&](float4 (&v)[4]) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int q = tp + 256 * i, row = q >> 3, c = q & 7;
+        const int gr = mt * BM + row;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gr < g.M) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + (long)gr * g.lda + (long)kb * BK + c * 4));
+      }
+    };
+    auto advance = [&]() {
+      if (++kb >= kb_end) {
+        w += gridDim.x;
+        live = w < n_items;
+        if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
+      }
+    };
+    float4 cur[4], nxt[4];
+    if (live) gload(cur);
+    uint32_t it = 0;
+    while (live) {
+      advance();
+      if (live) gload(nxt);
+      const int s = it % STAGES;
+      umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
+      uint8_t* a_hi = sm + s * STAGE_BYTES;
+      uint8_t* a_lo = a_hi + A_TILE_BYTES;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int q = tp + 256 * i, row = q >> 3, c = q & 7;
+        const int off = row * 128 + ((c ^ (row & 7)) << 4);
+        float4 h, l;
+        h.x = umma::to_tf32(cur[i].x); l.x = umma::to_tf32(cur[i].x - h.x);
+        h.y = umma::to_tf32(cur[i].y); l.y = umma::to_tf32(cur[i].y - h.y);
+        h.z = umma::to_tf32(cur[i].z); l.z = umma::to_tf32(cur[i].z - h.z);
+        h.w = umma::to_tf32(cur[i].w); l.w = umma::to_tf32(cur[i].w - h.w);
+        *reinterpret_cast<float4*>(a_hi + off) = h;
+        *reinterpret_cast<float4*>(a_lo + off) = l;
+      }
+      umma::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(FULL_A(s));
+#pragma unroll
+      for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+      ++it;
+    }
+  } else if (warp == WARP_BLOAD) {
+    // ===== B loader: one bulk copy per stage brings the pre-swizzled (hi|lo) tile =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+        int mt, nt, ks;
+        decode_item(g, w, mt, nt, ks);
+        const int kb0 = ks * g.kb_per_split, kb1 = min(kb0 + g.kb_per_split, g.kb_total);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % STAGES;
+          umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
+          umma::mbar_arrive_expect_tx(FULL_B(s), 2 * b_tile_bytes);
+          const float* src = g.Bimg + ((size_t)nt * g.kb_total + kb) * (size_t)(2 * g.NT * BK);
+          umma::bulk_g2s(base + s * STAGE_BYTES + 2 * A_TILE_BYTES, src, 2 * b_tile_bytes, FULL_B(s));
+        }
+      }
+    }
+  } else if (warp == WARP_MMA) {
+    // ===== MMA issuer (single thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = umma::idesc_tf32_m128((uint32_t)g.NT);
+      uint32_t it = 0, item = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+        int mt, nt, ks;
+        decode_item(g, w, mt, nt, ks);
+        const int kb0 = ks * g.kb_per_split, kb1 = min(kb0 + g.kb_per_split, g.kb_total);
+        const uint32_t acc = item & 1;
+        umma::mbar_wait(TEMPTY(acc), ((item >> 1) & 1) ^ 1);
+        umma::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * NT_MAX;
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          umma::mbar_wait(FULL_A(s), ph);
+          umma::mbar_wait(FULL_B(s), ph);
+          umma::tc_fence_after();
+          const uint32_t a_hi = base + s * STAGE_BYTES, a_lo = a_hi + A_TILE_BYTES;
+          const uint32_t b_hi = a_hi + 2 * A_TILE_BYTES, b_lo = b_hi + b_tile_bytes;
+#pragma unroll
+          for (int k = 0; k < BK / 8; ++k) {
+            const uint64_t dah = umma::smem_desc_sw128(a_hi + k * 32), dal = umma::smem_desc_sw128(a_lo + k * 32);
+            const uint64_t dbh = umma::smem_desc_sw128(b_hi + k * 32), dbl = umma::smem_desc_sw128(b_lo + k * 32);
+            umma::mma_tf32(d_tmem, dah, dbh, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma::mma_tf32(d_tmem, dal, dbh, idesc, 1u);
+            umma::mma_tf32(d_tmem, dah, dbl, idesc, 1u);
+          }
+          umma::mma_commit(EMPTY(s));   // smem slot is free once these MMAs have read it
+        }
+        umma::mma_commit(TFULL(acc));   // accumulator complete
+      }
+    }
+  } else {
+    // ===== epilogue warps 0..3: TMEM lanes 32*warp .. +31 =====
+    float* stg = staging + warp * STAGING_FLOATS;
+    uint32_t item = 0;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+      int mt, nt, ks;
+      decode_item(g, w, mt, nt, ks);
+      const uint32_t acc = item & 1;
+      umma::mbar_wait(TFULL(acc), (item >> 1) & 1);
+      umma::tc_fence_after();
+      float* Cw = g.C + (size_t)ks * g.split_stride;
+      const int row0 = mt * BM + warp * 32;
+      for (int c = 0; c < g.NT / 32; ++c) {
+        uint32_t r[32];
+        umma::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * NT_MAX + c * 32, r);
+        umma::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]);
+        __syncwarp();
+        const int col = nt * g.NT + c * 32 + lane;
+        const float bv = (g.bias && col < g.n_valid) ? g.bias[col] : 0.f;
+        if (col < g.n_valid) {
+#pragma unroll 8
+          for (int rr = 0; rr < 32; ++rr) {
+            const int row = row0 + rr;
+            if (row < g.M) Cw[(size_t)row * g.ldc + col] = stg[rr * 33 + lane] + bv;
+          }
+        }
+        __syncwarp();
+      }
+      umma::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(TEMPTY(acc));
+    }
+  }
+
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) {
+    __syncwarp();
+    umma::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+static inline float host_tf32(float x) {   // round to nearest (ties away) like cvt.rna.tf32.f32
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  if ((u & 0x7f800000u) != 0x7f800000u) u += 0x1000u;
+  u &= 0xffffe000u;
+  float r;
+  memcpy(&r, &u, 4);
+  return r;
+}
+
+void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int K, int NT) {
+  const int n_tiles = (rows + NT - 1) / NT, kbT = K / BK;
+  out.assign((size_t)n_tiles * kbT * 2 * NT * BK, 0.f);
+  for (int t = 0; t < n_tiles; ++t)
+    for (int kb = 0; kb < kbT; ++kb) {
+      float* hi = out.data() + ((size_t)t * kbT + kb) * 2 * NT * BK;
+      float* lo = hi + (size_t)NT * BK;
+      for (int r = 0; r < NT; ++r) {
+        const int gr = t * NT + r;
+        if (gr >= rows) continue;
+        for (int k = 0; k < BK; ++k) {
+          const float x = src[(size_t)gr * K + kb * BK + k];
+          const float h = host_tf32(x);
+          const int off = r * 32 + (((k >> 2) ^ (r & 7)) << 2) + (k & 3);
+          hi[off] = h;
+          lo[off] = host_tf32(x - h);
+        }
+      }
+    }
+}
+
+static int g_num_sms = 0;
+static int launch_umma(const GemmArgs& g, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    UUO_CUDA(cudaFuncSetAttribute(umma_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    int dev = 0;
+    UUO_CUDA(cudaGetDevice(&dev));
+    UUO_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+    attr_set = true;
+  }
+  const int items = g.m_tiles * g.n_tiles * g.k_splits;
+  umma_gemm_kernel<<<std::min(items, g_num_sms), NTHREADS, SMEM_BYTES, st>>>(g);
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+// number of deterministic K-split slabs the backward GEMM writes for F frames (<= UUO_NSPLIT_GC)
+int uuo_gcoef_splits(const uuo_model* m, int F) {
+  const int m_tiles = (F + BM - 1) / BM, kbT = m->NP / BK;
+  int want = std::max(1, std::min(UUO_NSPLIT_GC, (2 * 148 + m_tiles - 1) / m_tiles));
+  const int per = (kbT + want - 1) / want;
+  return (kbT + per - 1) / per;
+}
+
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+  GemmArgs g;
+  g.A = ws.coef; g.lda = m->KP; g.M = F;
+  g.Bimg = m->Bimg_fwd;
+  g.C = ws.vposed; g.ldc = m->NP; g.split_stride = 0;
+  g.bias = m->vt;
+  g.NT = 256; g.n_tiles = m->NP / 256; g.m_tiles = (F + BM - 1) / BM;
+  g.kb_total = m->KP / BK; g.k_splits = 1; g.kb_per_split = g.kb_total; g.n_valid = m->NP;
+  ProfScope ps_("vposed_gemm", st);
+  return launch_umma(g, st);
+}
+
+int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+  GemmArgs g;
+  g.A = ws.gvposed; g.lda = m->NP; g.M = F;
+  g.Bimg = m->Bimg_bwd;
+  g.C = ws.gcoef; g.ldc = m->KP; g.split_stride = (long)F * m->KP;
+  g.bias = nullptr;
+  g.NT = m->KP; g.n_tiles = 1; g.m_tiles = (F + BM - 1) / BM;
+  g.kb_total = m->NP / BK; g.k_splits = uuo_gcoef_splits(m, F);
+  g.kb_per_split = (g.kb_total + g.k_splits - 1) / g.k_splits; g.n_valid = m->KP;
+  ProfScope ps_("gcoef_gemm", st);
+  return launch_umma(g, st);
+}
