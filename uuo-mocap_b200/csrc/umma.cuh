@@ -119,4 +119,11 @@ __device__ __forceinline__ float to_tf32(float x) {
   return __uint_as_float(u);
 }
 
+// x = hi + lo with hi, lo representable in tf32 (round to nearest on the magnitude; inf/nan not expected)
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+  const float r = x - hi;
+  lo = __uint_as_float((__float_as_uint(r) + 0x1000u) & 0xffffe000u);
+}
+
 }  // namespace umma

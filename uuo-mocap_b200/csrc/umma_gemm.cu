@@ -28,7 +28,7 @@ constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES_MAX;   // 96 KB
 constexpr int EPI_WARPS = 4, PROD_WARPS = 8;
 constexpr int WARP_MMA = EPI_WARPS, WARP_BLOAD = EPI_WARPS + 1, WARP_PROD0 = EPI_WARPS + 2;
 constexpr int NTHREADS = (EPI_WARPS + 2 + PROD_WARPS) * 32;   // 448
-constexpr int STAGING_FLOATS = 32 * 33;              // per epilogue warp, padded transpose tile
+constexpr int STAGING_FLOATS = 32 * 32;              // per epilogue warp, XOR-swizzled transpose tile
 constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + EPI_WARPS * STAGING_FLOATS * 4 + 256;
 
 struct GemmArgs {
@@ -85,12 +85,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
   const uint32_t b_tile_bytes = (uint32_t)g.NT * BK * 4;
 
   if (warp >= WARP_PROD0) {
-    // ===== A producers: fp32 rows -> (hi, lo) SWIZZLE_128B images =====
+    // ===== A producers: fp32 rows -> (hi, lo) SWIZZLE_128B images; global loads run PF K-blocks ahead =====
+    constexpr int PF = 3;
     const int tp = threadIdx.x - WARP_PROD0 * 32;
     int w = blockIdx.x, mt = 0, nt = 0, ks = 0, kb = 0, kb_end = 0;
     bool live = w < n_items;
     if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
-    auto gload = [&](float4 (&v)[4]) {
+    auto gload = [&](float4 (&v)[4]) {   // loads the block the iterator points at, then advances it
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int q = tp + 256 * i, row = q >> 3, c = q & 7;
@@ -98,20 +99,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (gr < g.M) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + (long)gr * g.lda + (long)kb * BK + c * 4));
       }
-    };
-    auto advance = [&]() {
       if (++kb >= kb_end) {
         w += gridDim.x;
         live = w < n_items;
         if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
       }
     };
-    float4 cur[4], nxt[4];
-    if (live) gload(cur);
-    uint32_t it = 0;
-    while (live) {
-      advance();
-      if (live) gload(nxt);
+    float4 buf[PF][4], nw[4];
+    uint32_t loaded = 0, it = 0;
+#pragma unroll
+    for (int d = 0; d < PF; ++d)
+      if (live) { gload(buf[d]); ++loaded; }
+    while (it < loaded) {
+      const bool more = live;
+      if (more) { gload(nw); ++loaded; }
       const int s = it % STAGES;
       umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
       uint8_t* a_hi = sm + s * STAGE_BYTES;
@@ -121,10 +122,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         const int q = tp + 256 * i, row = q >> 3, c = q & 7;
         const int off = row * 128 + ((c ^ (row & 7)) << 4);
         float4 h, l;
-        h.x = umma::to_tf32(cur[i].x); l.x = umma::to_tf32(cur[i].x - h.x);
-        h.y = umma::to_tf32(cur[i].y); l.y = umma::to_tf32(cur[i].y - h.y);
-        h.z = umma::to_tf32(cur[i].z); l.z = umma::to_tf32(cur[i].z - h.z);
-        h.w = umma::to_tf32(cur[i].w); l.w = umma::to_tf32(cur[i].w - h.w);
+        umma::split_tf32(buf[0][i].x, h.x, l.x);
+        umma::split_tf32(buf[0][i].y, h.y, l.y);
+        umma::split_tf32(buf[0][i].z, h.z, l.z);
+        umma::split_tf32(buf[0][i].w, h.w, l.w);
         *reinterpret_cast<float4*>(a_hi + off) = h;
         *reinterpret_cast<float4*>(a_lo + off) = l;
       }
@@ -132,7 +133,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(FULL_A(s));
 #pragma unroll
-      for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+      for (int d = 0; d + 1 < PF; ++d)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) buf[d][i] = buf[d + 1][i];
+      if (more) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) buf[PF - 1][i] = nw[i];
+      }
       ++it;
     }
   } else if (warp == WARP_BLOAD) {
@@ -198,20 +205,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
       umma::tc_fence_after();
       float* Cw = g.C + (size_t)ks * g.split_stride;
       const int row0 = mt * BM + warp * 32;
+      const int nrows = min(32, g.M - row0);   // may be <= 0 for a ragged last tile
+      const int sub = lane >> 3, c4 = lane & 7;
       for (int c = 0; c < g.NT / 32; ++c) {
         uint32_t r[32];
         umma::tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * NT_MAX + c * 32, r);
         umma::tmem_ld_wait();
+        // lane = row: 8 x 16 B chunks, chunk position XOR (row & 7) -> conflict-free both ways
 #pragma unroll
-        for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]);
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(stg + lane * 32 + ((j ^ (lane & 7)) << 2)) =
+              make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                          __uint_as_float(r[4 * j + 3]));
         __syncwarp();
-        const int col = nt * g.NT + c * 32 + lane;
-        const float bv = (g.bias && col < g.n_valid) ? g.bias[col] : 0.f;
+        const int col = nt * g.NT + c * 32 + c4 * 4;
         if (col < g.n_valid) {
-#pragma unroll 8
-          for (int rr = 0; rr < 32; ++rr) {
-            const int row = row0 + rr;
-            if (row < g.M) Cw[(size_t)row * g.ldc + col] = stg[rr * 33 + lane] + bv;
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (g.bias) bv = __ldg(reinterpret_cast<const float4*>(g.bias + col));
+          float* dst = Cw + (size_t)row0 * g.ldc + col;
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr) {
+            const int rl = rr * 4 + sub;     // 4 rows per instruction, 8 lanes x 16 B = one 128 B line per row
+            float4 v = *reinterpret_cast<const float4*>(stg + rl * 32 + ((c4 ^ (rl & 7)) << 2));
+            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+            if (rl < nrows) *reinterpret_cast<float4*>(dst + (size_t)rl * g.ldc) = v;
           }
         }
         __syncwarp();
