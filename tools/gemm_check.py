@@ -18,6 +18,7 @@ from uuo_mocap_b200.smpl import SMPL, _as_struct
 
 def run(smpl, mb, simt):
     os.environ["UUO_GEMM_SIMT"] = "1" if simt else "0"
+    os.environ["UUO_SKIN_SIMT"] = "1" if simt else "0"
     rot = torch.from_numpy(mb["rot"]).cuda().requires_grad_(True)
     betas = torch.from_numpy(mb["betas"]).cuda().requires_grad_(True)
     transl = torch.from_numpy(mb["transl"]).cuda().requires_grad_(True)

@@ -36,6 +36,7 @@ struct uuo_model {
   int32_t* extra_ids;  // [NE]
   uint8_t* vflag;      // [V] 1 when some extra joint is this vertex
   float* Bimg_fwd;     // [NP/256][KP/32][2][256*32] tf32 hi|lo SWIZZLE_128B tiles of Bt   (umma_gemm.cu)
+  float* Wimg;         // [NP/384][2][128*32] tf32 hi|lo SWIZZLE_128B tiles of W (row = vertex, K = joint, padded to 32)
   float* Bimg_bwd;     // [1][NP/32][2][KP*32]       tf32 hi|lo SWIZZLE_128B tiles of Bmat
   // small tables passed by value to the FK kernels
   int8_t parents[UUO_MAX_J];
@@ -72,6 +73,7 @@ struct uuo_ws {
   float* gcoef;   // [NSPLIT_GC][F][KP]
   float* gbetas;  // [F][16]
   float* rowbuf;  // [F][R<=64][4]  scratch of the row-sparse paths
+  float* Aimg;    // [ceil(F/16)][2][192*32] tf32 hi|lo swizzled image of the relative transforms (skin_tc.cu)
   size_t total_floats;
 };
 
@@ -92,6 +94,7 @@ static inline uuo_ws carve_ws(const uuo_model* m, int F, void* base) {
   w.gcoef = take((size_t)UUO_NSPLIT_GC * F * m->KP);
   w.gbetas = take((size_t)F * 16);
   w.rowbuf = take((size_t)F * 64 * 4);
+  w.Aimg = take((size_t)((F + 15) / 16) * 2 * 192 * 32);
   w.total_floats = off;
   return w;
 }
@@ -148,6 +151,9 @@ int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts,
 int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int uuo_gcoef_splits(const uuo_model* m, int F);
+int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const float* g_joints, const float* transl,
+                   float* out, const uuo_ws& ws, cudaStream_t st);
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st);
 int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, const float* g_joints,

@@ -121,6 +121,11 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   uuo_build_b_image(img_fwd, Bt.data(), NP, KP, 256);
   uuo_build_b_image(img_bwd, Bmat.data(), KP, NP, KP);
   UUO_CHECK_ARG(KP <= 256 && KP % 16 == 0, "KP must be <= 256");
+  // skinning weights as an MMA operand: rows = the NP/3 vertex slots (zeros past V), K = 32 (J = 24 + zero pad)
+  std::vector<float> Wpad((size_t)(NP / 3) * 32, 0.f), img_w;
+  for (int v = 0; v < V; ++v)
+    for (int j = 0; j < J; ++j) Wpad[(size_t)v * 32 + j] = lbs_weights[(size_t)v * J + j];
+  uuo_build_b_image(img_w, Wpad.data(), NP / 3, 32, 128);
 
   std::vector<uint8_t> vflag(V, 0);
   std::vector<int32_t> ex(std::max(NE, 1), 0);
@@ -131,7 +136,8 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
       (rc = upload(&m->J0, J0)) || (rc = upload(&m->Jdirs, Jdirs)) || (rc = upload(&m->W, W)) ||
       (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
       (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag)) ||
-      (rc = upload(&m->Bimg_fwd, img_fwd)) || (rc = upload(&m->Bimg_bwd, img_bwd))) {
+      (rc = upload(&m->Bimg_fwd, img_fwd)) || (rc = upload(&m->Bimg_bwd, img_bwd)) ||
+      (rc = upload(&m->Wimg, img_w))) {
     uuo_model_destroy(m);
     return rc;
   }
@@ -143,7 +149,7 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
   if (!m) return;
   cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
   cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
-  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd);
+  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg);
   delete m;
 }
 

@@ -7,6 +7,13 @@
 // its split; g and v_posed tiles are staged [vertex][frame] in shared memory.
 #include "common.cuh"
 
+#include <stdlib.h>
+// UUO_SKIN_SIMT=1 selects the exact-fp32 SIMT kernels (debug cross-check of the tensor-core path, tools/gemm_check.py)
+static bool skin_simt() {
+  const char* e = getenv("UUO_SKIN_SIMT");
+  return e && e[0] == '1';
+}
+
 #define SK_THREADS 128
 #define SK_VPT 2
 #define SK_FB 16
@@ -263,11 +270,17 @@ __global__ void __launch_bounds__(GA_THREADS) skin_backward_A_kernel(
 
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st) {
+  if (!skin_simt()) {
+    int rc;
+    { ProfScope ps_("pack_transforms", st); if ((rc = launch_pack_transforms(m, F, ws, st))) return rc; }
+    { ProfScope ps_("skin_forward", st); if ((rc = launch_skin_tc(m, 0, F, ws.vposed, nullptr, transl, vertices, ws, st))) return rc; }
+  } else {
   const int vpb = SK_THREADS * SK_VPT;
   dim3 grid((m->V + vpb - 1) / vpb, (F + SK_FB - 1) / SK_FB);
   { ProfScope ps_("skin_forward", st);
   skin_forward_kernel<<<grid, SK_THREADS, 0, st>>>(m->W, ws.A, ws.vposed, m->NP, transl, F, m->V, vertices);
   } UUO_LAUNCH_CHECK();
+  }
   if (joints && m->NE > 0) {
     int n = F * m->NE;
     extra_joints_kernel<<<(n + 255) / 256, 256, 0, st>>>(vertices, m->extra_ids, F, m->V, m->J, m->NE, joints);
@@ -281,7 +294,11 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
   const int vpb = SK_THREADS * SK_VPT;
   // cover every column of the padded row so the pad is written as zeros
   dim3 grid1((m->NP / 3 + 1 + vpb - 1) / vpb, (F + SK_FB - 1) / SK_FB);
-  { ProfScope ps_("skin_backward_vposed", st);
+  if (!skin_simt()) {
+    int rc;
+    ProfScope ps_("skin_backward_vposed", st);
+    if ((rc = launch_skin_tc(m, 1, F, g_vertices, g_joints, nullptr, ws.gvposed, ws, st))) return rc;
+  } else { ProfScope ps_("skin_backward_vposed", st);
   skin_backward_vposed_kernel<<<grid1, SK_THREADS, 0, st>>>(m->W, ws.A, g_vertices, g_joints, m->extra_ids, m->vflag,
                                                             F, m->V, m->NE, m->NP, ws.gvposed);
   } UUO_LAUNCH_CHECK();

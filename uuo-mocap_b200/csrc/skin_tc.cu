@@ -1,0 +1,262 @@
+// Linear blend skinning on the tensor cores (lbs.py:237-250), dense J = 24 weights.
+//   T[f,v,e] = sum_j W[v,j] A[f,j,e]   (e = 12 entries of the 3x4 relative transform)
+// is the GEMM  D[v, (f,e)] = W[v, j] . Aimg[(f,e), j]^T  with M = 128 vertices (TMEM lane = vertex), N = 16 frames x 12
+// entries = 192 columns, K = 24 (three kind::tf32 k-steps), 3xTF32 split for fp32 accuracy.  The epilogue thread of
+// lane v reads its 12 blended entries per frame straight from TMEM and applies them:
+//   mode 0 (forward)      vertices[f,v] = T[:, :3] v_posed[f,v] + T[:, 3] + transl[f]
+//   mode 1 (d v_posed)    g_vposed[f,v] = T[:, :3]^T g[f,v]            (g = g_vertices + extra-joint rows of g_joints)
+// Operands: W is a model constant (pre-split, pre-swizzled image, resident in smem for the whole CTA); the transforms
+// are packed once per call into the same image format by pack_transforms_kernel and fetched with one 48 KB bulk copy
+// per frame tile.  Accumulators are double buffered in TMEM so MMAs of tile i+1 overlap the epilogue of tile i.
+#include <algorithm>
+
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace {
+
+constexpr int VT = 128;                 // vertices per tile (MMA M)
+constexpr int NF = 16;                  // frames per tile
+constexpr int NCOL = NF * 12;           // 192 accumulator columns (MMA N)
+constexpr int W_BYTES = VT * 128;       // 16 KB per half (hi / lo)
+constexpr int T_BYTES = NCOL * 128;     // 24 KB per half
+constexpr int STAGES = 3;
+constexpr int EPI_WARPS = 8;
+constexpr int WARP_MMA = EPI_WARPS, WARP_LOAD = EPI_WARPS + 1;
+constexpr int NTHREADS = (EPI_WARPS + 2) * 32;   // 320
+constexpr int SMEM_BYTES = 1024 + 2 * W_BYTES + STAGES * 2 * T_BYTES + 256;
+
+// Aimg[ft][half][row = fl*12 + e][32] (SWIZZLE_128B), element k = joint
+__global__ void pack_transforms_kernel(const float* __restrict__ A, int F, int n_ftiles, float* __restrict__ Aimg) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // one 16 B chunk: (ft, row, c)
+  if (i >= n_ftiles * NCOL * 8) return;
+  const int c = i & 7, row = (i >> 3) % NCOL, ft = (i >> 3) / NCOL;
+  const int fl = row / 12, e = row % 12, f = ft * NF + fl;
+  float4 h = make_float4(0.f, 0.f, 0.f, 0.f), l = h;
+  if (f < F && c < UUO_SKIN_J / 4) {
+    const float* src = A + ((size_t)f * UUO_SKIN_J + c * 4) * 12 + e;
+    umma::split_tf32(src[0], h.x, l.x);
+    umma::split_tf32(src[12], h.y, l.y);
+    umma::split_tf32(src[24], h.z, l.z);
+    umma::split_tf32(src[36], h.w, l.w);
+  }
+  float* hi = Aimg + (size_t)ft * 2 * NCOL * 32;
+  const int off = row * 32 + ((c ^ (row & 7)) << 2);
+  *reinterpret_cast<float4*>(hi + off) = h;
+  *reinterpret_cast<float4*>(hi + NCOL * 32 + off) = l;
+}
+
+struct SkinArgs {
+  const float* Wimg;      // [vtiles][2][128*32]
+  const float* Aimg;      // [ftiles][2][192*32]
+  const float* in;        // mode 0: v_posed [F][NP];  mode 1: g_vertices [F][V][3] (may be null)
+  const float* g_joints;  // mode 1: [F][J+NE][3] or null
+  const int32_t* extra_ids;
+  const uint8_t* vflag;
+  const float* transl;    // mode 0: [F][3] or null
+  float* out;             // mode 0: vertices [F][V][3];  mode 1: g_vposed [F][NP]
+  int F, V, NP, NE, J, n_ftiles, ft_per_chunk;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = umma::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (base - raw);
+  const uint32_t w_smem = base, t_smem = base + 2 * W_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + 2 * W_BYTES + STAGES * 2 * T_BYTES);
+  // bars: [0,S) full, [S,2S) empty, [2S,2S+2) tmem_full, [2S+2,2S+4) tmem_empty, [2S+4] W loaded
+  const uint32_t bar0 = umma::smem_u32(bars);
+  auto FULL = [&](int s) { return bar0 + 8u * s; };
+  auto EMPTY = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto TFULL = [&](int q) { return bar0 + 8u * (2 * STAGES + q); };
+  auto TEMPTY = [&](int q) { return bar0 + 8u * (2 * STAGES + 2 + q); };
+  const uint32_t WBAR = bar0 + 8u * (2 * STAGES + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 5);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int vt = blockIdx.x;
+  const int ft0 = blockIdx.y * a.ft_per_chunk, ft1 = min(ft0 + a.ft_per_chunk, a.n_ftiles);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { umma::mbar_init(FULL(s), 1); umma::mbar_init(EMPTY(s), 1); }
+    for (int q = 0; q < 2; ++q) { umma::mbar_init(TFULL(q), 1); umma::mbar_init(TEMPTY(q), EPI_WARPS); }
+    umma::mbar_init(WBAR, 1);
+    umma::fence_barrier_init();
+  }
+  if (warp == WARP_MMA) umma::tmem_alloc(umma::smem_u32(tmem_slot), 512);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == WARP_LOAD) {
+    if (lane == 0) {
+      umma::mbar_arrive_expect_tx(WBAR, 2 * W_BYTES);
+      umma::bulk_g2s(w_smem, a.Wimg + (size_t)vt * 2 * VT * 32, 2 * W_BYTES, WBAR);
+      uint32_t it = 0;
+      for (int ft = ft0; ft < ft1; ++ft, ++it) {
+        const int s = it % STAGES;
+        umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
+        umma::mbar_arrive_expect_tx(FULL(s), 2 * T_BYTES);
+        umma::bulk_g2s(t_smem + s * 2 * T_BYTES, a.Aimg + (size_t)ft * 2 * NCOL * 32, 2 * T_BYTES, FULL(s));
+      }
+    }
+  } else if (warp == WARP_MMA) {
+    if (lane == 0) {
+      const uint32_t idesc = umma::idesc_tf32_m128(NCOL);
+      umma::mbar_wait(WBAR, 0);
+      uint32_t it = 0;
+      for (int ft = ft0; ft < ft1; ++ft, ++it) {
+        const int s = it % STAGES;
+        const uint32_t acc = it & 1;
+        umma::mbar_wait(TEMPTY(acc), ((it >> 1) & 1) ^ 1);
+        umma::mbar_wait(FULL(s), (it / STAGES) & 1);
+        umma::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        const uint32_t t_hi = t_smem + s * 2 * T_BYTES, t_lo = t_hi + T_BYTES;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const uint64_t dwh = umma::smem_desc_sw128(w_smem + k * 32), dwl = umma::smem_desc_sw128(w_smem + W_BYTES + k * 32);
+          const uint64_t dth = umma::smem_desc_sw128(t_hi + k * 32), dtl = umma::smem_desc_sw128(t_lo + k * 32);
+          umma::mma_tf32(d_tmem, dwh, dth, idesc, k > 0 ? 1u : 0u);
+          umma::mma_tf32(d_tmem, dwl, dth, idesc, 1u);
+          umma::mma_tf32(d_tmem, dwh, dtl, idesc, 1u);
+        }
+        umma::mma_commit(EMPTY(s));
+        umma::mma_commit(TFULL(acc));
+      }
+    }
+  } else {
+    // ===== epilogue: warp quadrant = TMEM lanes, warp group = which 8 of the tile's 16 frames =====
+    const int gq = warp >> 2, quad = warp & 3;
+    const int v = vt * VT + quad * 32 + lane;
+    const bool v_ok = v < a.V;
+    // extra-joint rows of g_joints that alias this vertex (vertex_joint_selector.py:73-80), as a bit mask over e
+    unsigned long long emask = 0ull;
+    if (MODE == 1 && v_ok && a.g_joints && a.vflag[v])
+      for (int e = 0; e < a.NE && e < 64; ++e)
+        if (a.extra_ids[e] == v) emask |= 1ull << e;
+    auto load_x = [&](int ft, float (&x)[8][3]) {
+      const int fbase = ft * NF + gq * 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int f = fbase + i;
+        x[i][0] = x[i][1] = x[i][2] = 0.f;
+        if (ft < ft1 && f < a.F && v_ok) {
+          if (MODE == 0) {
+            const float* p = a.in + (size_t)f * a.NP + (size_t)v * 3;
+            x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
+          } else {
+            if (a.in) {
+              const float* p = a.in + ((size_t)f * a.V + v) * 3;
+              x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
+            }
+            unsigned long long mk = emask;
+            while (mk) {
+              const int e = __ffsll((long long)mk) - 1;
+              mk &= mk - 1;
+              const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e) * 3;
+              x[i][0] += q[0]; x[i][1] += q[1]; x[i][2] += q[2];
+            }
+          }
+        }
+      }
+    };
+    uint32_t it = 0;
+    float x[8][3], xn[8][3];
+    load_x(ft0, x);
+    for (int ft = ft0; ft < ft1; ++ft, ++it) {
+      const int fbase = ft * NF + gq * 8;
+      load_x(ft + 1, xn);   // next tile's inputs are in flight while this tile's accumulator is drained
+      const uint32_t acc = it & 1;
+      umma::mbar_wait(TFULL(acc), (it >> 1) & 1);
+      umma::tc_fence_after();
+#pragma unroll
+      for (int st = 0; st < 2; ++st) {
+        uint32_t r[48];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * 256 + (gq * 8 + st * 4) * 12;
+        umma::tmem_ld16(taddr, r);
+        umma::tmem_ld16(taddr + 16, r + 16);
+        umma::tmem_ld16(taddr + 32, r + 32);
+        umma::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = st * 4 + k, f = fbase + i;
+          float T[12];
+#pragma unroll
+          for (int e = 0; e < 12; ++e) T[e] = __uint_as_float(r[k * 12 + e]);
+          if (f < a.F) {
+            if (MODE == 0) {
+              if (v_ok) {
+                float tr[3] = {0.f, 0.f, 0.f};
+                if (a.transl) { tr[0] = a.transl[(size_t)f * 3]; tr[1] = a.transl[(size_t)f * 3 + 1]; tr[2] = a.transl[(size_t)f * 3 + 2]; }
+                float* o = a.out + ((size_t)f * a.V + v) * 3;
+#pragma unroll
+                for (int rr = 0; rr < 3; ++rr)
+                  o[rr] = (T[rr * 4] * x[i][0] + T[rr * 4 + 1] * x[i][1] + T[rr * 4 + 2] * x[i][2] + T[rr * 4 + 3]) + tr[rr];
+              }
+            } else {
+              // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads
+              float* o = a.out + (size_t)f * a.NP + (size_t)v * 3;
+#pragma unroll
+              for (int c = 0; c < 3; ++c) o[c] = T[c] * x[i][0] + T[4 + c] * x[i][1] + T[8 + c] * x[i][2];
+            }
+          }
+        }
+      }
+      umma::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) umma::mbar_arrive(TEMPTY(acc));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { x[i][0] = xn[i][0]; x[i][1] = xn[i][1]; x[i][2] = xn[i][2]; }
+    }
+  }
+
+  umma::tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) {
+    __syncwarp();
+    umma::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+  const int n_ft = (F + NF - 1) / NF;
+  const int n = n_ft * NCOL * 8;
+  pack_transforms_kernel<<<(n + 255) / 256, 256, 0, st>>>(ws.A, F, n_ft, ws.Aimg);
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const float* g_joints, const float* transl,
+                   float* out, const uuo_ws& ws, cudaStream_t st) {
+  static bool attr_set = false;
+  static int num_sms = 148;
+  if (!attr_set) {
+    UUO_CUDA(cudaFuncSetAttribute(skin_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    UUO_CUDA(cudaFuncSetAttribute(skin_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    int dev = 0;
+    UUO_CUDA(cudaGetDevice(&dev));
+    UUO_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    attr_set = true;
+  }
+  SkinArgs a;
+  a.Wimg = m->Wimg; a.Aimg = ws.Aimg; a.in = in; a.g_joints = g_joints; a.extra_ids = m->extra_ids; a.vflag = m->vflag;
+  a.transl = transl; a.out = out;
+  a.F = F; a.V = m->V; a.NP = m->NP; a.NE = m->NE; a.J = m->J;
+  a.n_ftiles = (F + NF - 1) / NF;
+  const int vtiles = m->NP / 3 / VT;
+  // frame chunks: about three waves of CTAs, each walking a contiguous run of frame tiles with W resident
+  int chunks = std::max(1, std::min(a.n_ftiles, (3 * num_sms) / vtiles));
+  a.ft_per_chunk = (a.n_ftiles + chunks - 1) / chunks;
+  chunks = (a.n_ftiles + a.ft_per_chunk - 1) / a.ft_per_chunk;
+  dim3 grid(vtiles, chunks);
+  if (mode == 0) skin_tc_kernel<0><<<grid, NTHREADS, SMEM_BYTES, st>>>(a);
+  else skin_tc_kernel<1><<<grid, NTHREADS, SMEM_BYTES, st>>>(a);
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
