@@ -133,39 +133,56 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
     const int gq = warp >> 2, quad = warp & 3;
     const int v = vt * VT + quad * 32 + lane;
     const bool v_ok = v < a.V;
-    // extra-joint rows of g_joints that alias this vertex (vertex_joint_selector.py:73-80), as a bit mask over e
-    unsigned long long emask = 0ull;
+    // extra-joint row of g_joints that aliases this vertex (vertex_joint_selector.py:73-80): first match e0, and a
+    // mask of further matches (none for SMPL, where the 21 extra joints are distinct vertices)
+    int e0 = -1;
+    unsigned long long emore = 0ull;
     if (MODE == 1 && v_ok && a.g_joints && a.vflag[v])
       for (int e = 0; e < a.NE && e < 64; ++e)
-        if (a.extra_ids[e] == v) emask |= 1ull << e;
-    auto load_x = [&](int ft, float (&x)[8][3]) {
+        if (a.extra_ids[e] == v) { if (e0 < 0) e0 = e; else emore |= 1ull << e; }
+    // x[i][0..2] = per-frame input of the vertex; x[i][3..5] = transl (mode 0)
+    auto load_x = [&](int ft, float (&x)[8][6]) {
       const int fbase = ft * NF + gq * 8;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int f = fbase + i;
-        x[i][0] = x[i][1] = x[i][2] = 0.f;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) x[i][c] = 0.f;
         if (ft < ft1 && f < a.F && v_ok) {
           if (MODE == 0) {
             const float* p = a.in + (size_t)f * a.NP + (size_t)v * 3;
             x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
+            if (a.transl) {
+              const float* t = a.transl + (size_t)f * 3;
+              x[i][3] = __ldg(t); x[i][4] = __ldg(t + 1); x[i][5] = __ldg(t + 2);
+            }
           } else {
             if (a.in) {
               const float* p = a.in + ((size_t)f * a.V + v) * 3;
               x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
             }
-            unsigned long long mk = emask;
-            while (mk) {
-              const int e = __ffsll((long long)mk) - 1;
-              mk &= mk - 1;
-              const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e) * 3;
-              x[i][0] += q[0]; x[i][1] += q[1]; x[i][2] += q[2];
+            if (e0 >= 0) {
+              const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e0) * 3;
+              x[i][3] = __ldg(q); x[i][4] = __ldg(q + 1); x[i][5] = __ldg(q + 2);
             }
+          }
+        }
+      }
+      if (MODE == 1 && emore) {   // rare: several extra joints on one vertex
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int f = fbase + i;
+          if (!(ft < ft1 && f < a.F)) continue;
+          for (unsigned long long mk = emore; mk; mk &= mk - 1) {
+            const int e = __ffsll((long long)mk) - 1;
+            const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e) * 3;
+            x[i][3] += q[0]; x[i][4] += q[1]; x[i][5] += q[2];
           }
         }
       }
     };
     uint32_t it = 0;
-    float x[8][3], xn[8][3];
+    float x[8][6], xn[8][6];
     load_x(ft0, x);
     for (int ft = ft0; ft < ft1; ++ft, ++it) {
       const int fbase = ft * NF + gq * 8;
@@ -190,18 +207,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
           if (f < a.F) {
             if (MODE == 0) {
               if (v_ok) {
-                float tr[3] = {0.f, 0.f, 0.f};
-                if (a.transl) { tr[0] = a.transl[(size_t)f * 3]; tr[1] = a.transl[(size_t)f * 3 + 1]; tr[2] = a.transl[(size_t)f * 3 + 2]; }
                 float* o = a.out + ((size_t)f * a.V + v) * 3;
 #pragma unroll
                 for (int rr = 0; rr < 3; ++rr)
-                  o[rr] = (T[rr * 4] * x[i][0] + T[rr * 4 + 1] * x[i][1] + T[rr * 4 + 2] * x[i][2] + T[rr * 4 + 3]) + tr[rr];
+                  o[rr] = (T[rr * 4] * x[i][0] + T[rr * 4 + 1] * x[i][1] + T[rr * 4 + 2] * x[i][2] + T[rr * 4 + 3]) + x[i][3 + rr];
               }
             } else {
               // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads
               float* o = a.out + (size_t)f * a.NP + (size_t)v * 3;
 #pragma unroll
-              for (int c = 0; c < 3; ++c) o[c] = T[c] * x[i][0] + T[4 + c] * x[i][1] + T[8 + c] * x[i][2];
+              const float g0 = x[i][0] + x[i][3], g1 = x[i][1] + x[i][4], g2 = x[i][2] + x[i][5];
+#pragma unroll
+              for (int c = 0; c < 3; ++c) o[c] = T[c] * g0 + T[4 + c] * g1 + T[8 + c] * g2;
             }
           }
         }
@@ -210,7 +227,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(TEMPTY(acc));
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { x[i][0] = xn[i][0]; x[i][1] = xn[i][1]; x[i][2] = xn[i][2]; }
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) x[i][c] = xn[i][c];
     }
   }
 
