@@ -37,6 +37,7 @@ struct uuo_model {
   uint8_t* vflag;      // [V] 1 when some extra joint is this vertex
   float* Bimg_fwd;     // [NP/256][KP/32][2][256*32] tf32 hi|lo SWIZZLE_128B tiles of Bt   (umma_gemm.cu)
   float* Wimg;         // [NP/384][2][128*32] tf32 hi|lo SWIZZLE_128B tiles of W (row = vertex, K = joint, padded to 32)
+  float* WTimg;        // [NP/96][2][32*32] tf32 hi|lo tiles of [W | 1]^T (row = joint, K = vertex)  (skin_bwdA_tc.cu)
   float* Bimg_bwd;     // [1][NP/32][2][KP*32]       tf32 hi|lo SWIZZLE_128B tiles of Bmat
   // small tables passed by value to the FK kernels
   int8_t parents[UUO_MAX_J];
@@ -154,6 +155,10 @@ int uuo_gcoef_splits(const uuo_model* m, int F);
 int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const float* g_joints, const float* transl,
                    float* out, const uuo_ws& ws, cudaStream_t st);
+int launch_skin_bwdA_tc(const uuo_model* m, int F, const float* g_vertices, const float* g_joints, const uuo_ws& ws,
+                        cudaStream_t st);
+int uuo_bwdA_splits(const uuo_model* m);
+int uuo_ga_parts(const uuo_model* m);
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st);
 int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, const float* g_joints,

@@ -126,8 +126,15 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   for (int v = 0; v < V; ++v)
     for (int j = 0; j < J; ++j) Wpad[(size_t)v * 32 + j] = lbs_weights[(size_t)v * J + j];
   uuo_build_b_image(img_w, Wpad.data(), NP / 3, 32, 128);
+  // [W | 1]^T for the d(A) contraction over vertices: 32 rows (24 joints, a ones row that yields sum_v g, zero pad)
+  std::vector<float> WT((size_t)32 * (NP / 3), 0.f), img_wt;
+  for (int v = 0; v < V; ++v) {
+    for (int j = 0; j < J; ++j) WT[(size_t)j * (NP / 3) + v] = lbs_weights[(size_t)v * J + j];
+    WT[(size_t)J * (NP / 3) + v] = 1.f;
+  }
+  uuo_build_b_image(img_wt, WT.data(), 32, NP / 3, 32);
 
-  std::vector<uint8_t> vflag(V, 0);
+  std::vector<uint8_t> vflag(NP / 3, 0);   // padded: read 4 flags at a time
   std::vector<int32_t> ex(std::max(NE, 1), 0);
   for (int e = 0; e < NE; ++e) { ex[e] = extra_joint_ids[e]; vflag[ex[e]] = 1; }
 
@@ -137,7 +144,7 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
       (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
       (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag)) ||
       (rc = upload(&m->Bimg_fwd, img_fwd)) || (rc = upload(&m->Bimg_bwd, img_bwd)) ||
-      (rc = upload(&m->Wimg, img_w))) {
+      (rc = upload(&m->Wimg, img_w)) || (rc = upload(&m->WTimg, img_wt))) {
     uuo_model_destroy(m);
     return rc;
   }
@@ -149,7 +156,7 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
   if (!m) return;
   cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
   cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
-  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg);
+  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg); cudaFree(m->WTimg);
   delete m;
 }
 

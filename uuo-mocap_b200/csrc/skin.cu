@@ -14,6 +14,9 @@ static bool skin_simt() {
   return e && e[0] == '1';
 }
 
+// number of d(A) partial slabs launch_skin_backward writes to ws.gA
+int uuo_ga_parts(const uuo_model* m) { return skin_simt() ? UUO_NSPLIT_GA : uuo_bwdA_splits(m); }
+
 #define SK_THREADS 128
 #define SK_VPT 2
 #define SK_FB 16
@@ -302,6 +305,10 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
   skin_backward_vposed_kernel<<<grid1, SK_THREADS, 0, st>>>(m->W, ws.A, g_vertices, g_joints, m->extra_ids, m->vflag,
                                                             F, m->V, m->NE, m->NP, ws.gvposed);
   } UUO_LAUNCH_CHECK();
+  if (!skin_simt()) {
+    ProfScope ps_("skin_backward_A", st);
+    return launch_skin_bwdA_tc(m, F, g_vertices, g_joints, ws, st);
+  }
   const int vps = ((m->V + UUO_NSPLIT_GA - 1) / UUO_NSPLIT_GA + GA_VC - 1) / GA_VC * GA_VC;
   dim3 grid2((F + GA_FB - 1) / GA_FB, UUO_NSPLIT_GA);
   { ProfScope ps_("skin_backward_A", st);
