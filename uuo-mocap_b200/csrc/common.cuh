@@ -70,7 +70,7 @@ struct uuo_ws {
   float* A;       // [F][J][12]   rows of [R | t]   (lbs.py:403-405 relative transforms, 3x4 part)
   float* vposed;  // [F][NP]
   float* gvposed; // [F][NP]
-  float* gA;      // [NSPLIT_GA][F][GA_STRIDE]
+  float* gA;      // [<= 2*NSPLIT_GA][F][GA_STRIDE]
   float* gcoef;   // [NSPLIT_GC][F][KP]
   float* gbetas;  // [F][16]
   float* rowbuf;  // [F][R<=64][4]  scratch of the row-sparse paths
@@ -91,7 +91,7 @@ static inline uuo_ws carve_ws(const uuo_model* m, int F, void* base) {
   w.A = take((size_t)F * m->J * 12);
   w.vposed = take((size_t)F * m->NP);
   w.gvposed = take((size_t)F * m->NP);
-  w.gA = take((size_t)UUO_NSPLIT_GA * F * UUO_GA_STRIDE);
+  w.gA = take((size_t)2 * UUO_NSPLIT_GA * F * UUO_GA_STRIDE);   // tensor-core path: hi and lo slab per vertex split
   w.gcoef = take((size_t)UUO_NSPLIT_GC * F * m->KP);
   w.gbetas = take((size_t)F * 16);
   w.rowbuf = take((size_t)F * 64 * 4);

@@ -15,7 +15,7 @@ static bool skin_simt() {
 }
 
 // number of d(A) partial slabs launch_skin_backward writes to ws.gA
-int uuo_ga_parts(const uuo_model* m) { return skin_simt() ? UUO_NSPLIT_GA : uuo_bwdA_splits(m); }
+int uuo_ga_parts(const uuo_model* m) { return skin_simt() ? UUO_NSPLIT_GA : 2 * uuo_bwdA_splits(m); }
 
 #define SK_THREADS 128
 #define SK_VPT 2

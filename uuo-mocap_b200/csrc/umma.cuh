@@ -131,9 +131,16 @@ __device__ __forceinline__ float to_tf32(float x) {
 
 // x = hi + lo with hi, lo representable in tf32 (round to nearest on the magnitude; inf/nan not expected)
 __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+#ifdef UUO_SPLIT_ROUND
   hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
   const float r = x - hi;
   lo = __uint_as_float((__float_as_uint(r) + 0x1000u) & 0xffffe000u);
+#else
+  // kind::tf32 ignores the low 13 mantissa bits of its fp32 operands (truncation), so the raw value IS the hi term
+  // and the remainder x - trunc(x) is exact in fp32; two ALU ops per element instead of five.
+  hi = x;
+  lo = x - __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+#endif
 }
 
 }  // namespace umma
