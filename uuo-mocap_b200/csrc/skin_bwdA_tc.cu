@@ -193,20 +193,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
       }
     }
   } else if (warp == WARP_MMA) {
-    if (lane == 0) {
-      const uint32_t idesc = idesc_tf32_m64(NQ);
-      uint32_t it = 0;
-      for (int item = 0; item < my_items; ++item) {
-        const uint32_t acc = item & 1;
-        umma::mbar_wait(TEMPTY(acc), ((item >> 1) & 1) ^ 1);
+    // the warp stays converged; one elected lane issues
+    const uint32_t idesc = idesc_tf32_m64(NQ);
+    uint32_t it = 0;
+    for (int item = 0; item < my_items; ++item) {
+      const uint32_t acc = item & 1;
+      umma::mbar_wait(TEMPTY(acc), ((item >> 1) & 1) ^ 1);
+      const uint32_t d_tmem = tmem_base + acc * 256;
+      for (int kl = 0; kl < a.kb_per_split; ++kl, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        umma::mbar_wait(FULL_Q(s), ph);
+        umma::mbar_wait(FULL_W(s), ph);
         umma::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * 256;
-        for (int kl = 0; kl < a.kb_per_split; ++kl, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          umma::mbar_wait(FULL_Q(s), ph);
-          umma::mbar_wait(FULL_W(s), ph);
-          umma::tc_fence_after();
+        if (umma::elect_one()) {
           const uint32_t q_hi = base + s * STAGE_BYTES, q_lo = q_hi + Q_BYTES, ww = q_hi + 2 * Q_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / 8; ++k) {
@@ -215,8 +215,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
             umma::mma_tf32(d_tmem, dw, umma::smem_desc_sw128(q_lo + k * 32), idesc, 1u);
           }
           umma::mma_commit(EMPTY(s));
+          if (kl + 1 == a.kb_per_split) umma::mma_commit(TFULL(acc));
         }
-        umma::mma_commit(TFULL(acc));
+        __syncwarp();
       }
     }
   } else {

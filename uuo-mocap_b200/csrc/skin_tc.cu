@@ -104,16 +104,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
       }
     }
   } else if (warp == WARP_MMA) {
-    if (lane == 0) {
-      const uint32_t idesc = umma::idesc_tf32_m128(NCOL);
-      umma::mbar_wait(WBAR, 0);
-      uint32_t it = 0;
-      for (int ft = ft0; ft < ft1; ++ft, ++it) {
-        const int s = it % STAGES;
-        const uint32_t acc = it & 1;
-        umma::mbar_wait(TEMPTY(acc), ((it >> 1) & 1) ^ 1);
-        umma::mbar_wait(FULL(s), (it / STAGES) & 1);
-        umma::tc_fence_after();
+    // the warp stays converged; one elected lane issues
+    const uint32_t idesc = umma::idesc_tf32_m128(NCOL);
+    umma::mbar_wait(WBAR, 0);
+    uint32_t it = 0;
+    for (int ft = ft0; ft < ft1; ++ft, ++it) {
+      const int s = it % STAGES;
+      const uint32_t acc = it & 1;
+      umma::mbar_wait(TEMPTY(acc), ((it >> 1) & 1) ^ 1);
+      umma::mbar_wait(FULL(s), (it / STAGES) & 1);
+      umma::tc_fence_after();
+      if (umma::elect_one()) {
         const uint32_t d_tmem = tmem_base + acc * 256;
         const uint32_t t_hi = t_smem + s * 2 * T_BYTES, t_lo = t_hi + T_BYTES;
 #pragma unroll
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
         umma::mma_commit(EMPTY(s));
         umma::mma_commit(TFULL(acc));
       }
+      __syncwarp();
     }
   } else {
     // ===== epilogue: warp quadrant = TMEM lanes, warp group = which 8 of the tile's 16 frames =====
@@ -215,7 +217,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
             } else {
               // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads
               float* o = a.out + (size_t)f * a.NP + (size_t)v * 3;
-#pragma unroll
               const float g0 = x[i][0] + x[i][3], g1 = x[i][1] + x[i][4], g2 = x[i][2] + x[i][5];
 #pragma unroll
               for (int c = 0; c < 3; ++c) o[c] = T[c] * g0 + T[4 + c] * g1 + T[8 + c] * g2;

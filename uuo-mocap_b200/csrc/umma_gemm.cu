@@ -160,24 +160,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
       }
     }
   } else if (warp == WARP_MMA) {
-    // ===== MMA issuer (single thread) =====
-    if (lane == 0) {
-      const uint32_t idesc = umma::idesc_tf32_m128((uint32_t)g.NT);
-      uint32_t it = 0, item = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
-        int mt, nt, ks;
-        decode_item(g, w, mt, nt, ks);
-        const int kb0 = ks * g.kb_per_split, kb1 = min(kb0 + g.kb_per_split, g.kb_total);
-        const uint32_t acc = item & 1;
-        umma::mbar_wait(TEMPTY(acc), ((item >> 1) & 1) ^ 1);
+    // ===== MMA issuer: the warp stays converged, one elected lane issues (uniform-register operands) =====
+    const uint32_t idesc = umma::idesc_tf32_m128((uint32_t)g.NT);
+    uint32_t it = 0, item = 0;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+      int mt, nt, ks;
+      decode_item(g, w, mt, nt, ks);
+      const int kb0 = ks * g.kb_per_split, kb1 = min(kb0 + g.kb_per_split, g.kb_total);
+      const uint32_t acc = item & 1;
+      umma::mbar_wait(TEMPTY(acc), ((item >> 1) & 1) ^ 1);
+      const uint32_t d_tmem = tmem_base + acc * NT_MAX;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        umma::mbar_wait(FULL_A(s), ph);
+        umma::mbar_wait(FULL_B(s), ph);
         umma::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * NT_MAX;
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const int s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          umma::mbar_wait(FULL_A(s), ph);
-          umma::mbar_wait(FULL_B(s), ph);
-          umma::tc_fence_after();
+        if (umma::elect_one()) {
           const uint32_t a_hi = base + s * STAGE_BYTES, a_lo = a_hi + A_TILE_BYTES;
           const uint32_t b_hi = a_hi + 2 * A_TILE_BYTES, b_lo = b_hi + b_tile_bytes;
 #pragma unroll
@@ -188,9 +187,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
             umma::mma_tf32(d_tmem, dal, dbh, idesc, 1u);
             umma::mma_tf32(d_tmem, dah, dbl, idesc, 1u);
           }
-          umma::mma_commit(EMPTY(s));   // smem slot is free once these MMAs have read it
+          umma::mma_commit(EMPTY(s));                     // smem slot is free once these MMAs have read it
+          if (kb + 1 == kb1) umma::mma_commit(TFULL(acc));   // accumulator complete
         }
-        umma::mma_commit(TFULL(acc));   // accumulator complete
+        __syncwarp();
       }
     }
   } else {
