@@ -147,3 +147,30 @@ def test_partial_grads_and_errors(layers):
             root_orient=torch.zeros(1, 1, 3, 3).cuda(), trans=torch.zeros(1, 3).cuda())
     assert inf.get_lbs_weights().shape == (6890, 24)
     assert inf.smpl.parents.shape == (24,)
+
+
+def test_unaligned_caller_tensors(layers):
+    """Caller tensors are only 4-byte aligned in general (views into larger buffers): the vectorised / async-copy
+    paths must give bit-identical results for aligned and shifted storage."""
+    from uuo_mocap_b200 import synthetic
+    smpl, _ = layers["dense"]
+    F = 37
+    mb = synthetic.make_lbs_microbench(F, seed=21)
+
+    def shifted(a, k):
+        flat = torch.zeros(a.size + 8, device="cuda")
+        flat[k:k + a.size] = torch.from_numpy(a.reshape(-1)).cuda()
+        return flat[k:k + a.size].view(*a.shape)
+
+    outs = []
+    for k in (0, 1, 3):
+        rot = shifted(mb["rot"], k).requires_grad_(True)
+        betas = shifted(mb["betas"], k).requires_grad_(True)
+        transl = shifted(mb["transl"], k).requires_grad_(True)
+        o = smpl(betas=betas, body_pose=rot[:, 1:], global_orient=rot[:, :1], transl=transl, pose2rot=False)
+        gv, gj = shifted(mb["g_vertices"], k), shifted(mb["g_joints"], k)
+        grads = torch.autograd.grad([o.vertices, o.joints], [rot, betas, transl], grad_outputs=[gv, gj])
+        outs.append([t.detach().cpu() for t in (o.vertices, o.joints) + tuple(grads)])
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            assert torch.equal(a, b)

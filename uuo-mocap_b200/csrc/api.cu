@@ -40,7 +40,7 @@ extern "C" int uuo_lbs_backward(const uuo_model* m, const float* betas, int beta
   int n_gc = 0;
   if ((rc = launch_gcoef_gemm(m, F, ws, &n_gc, st))) return rc;
   return launch_fk_backward(m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, F, g_joints, ws,
-                            uuo_ga_parts(m), n_gc, nullptr, g_betas, g_global_orient, g_body_pose, g_yaw,
+                            uuo_ga_parts(m, g_joints != nullptr), n_gc, nullptr, g_betas, g_global_orient, g_body_pose, g_yaw,
                             g_transl, st);
 }
 

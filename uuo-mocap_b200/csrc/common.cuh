@@ -35,6 +35,10 @@ struct uuo_model {
   float* ell_w;   // [V][4]
   int32_t* extra_ids;  // [NE]
   uint8_t* vflag;      // [V] 1 when some extra joint is this vertex
+  int NU;              // distinct vertices among the extra joints
+  int32_t* xu_vert;    // [NU]   the vertex
+  int32_t* xu_start;   // [NU+1] CSR into xu_list
+  int32_t* xu_list;    // [NE]   extra-joint indices e aliasing that vertex
   float* Bimg_fwd;     // [NP/256][KP/32][2][256*32] tf32 hi|lo SWIZZLE_128B tiles of Bt   (umma_gemm.cu)
   float* Wimg;         // [NP/384][2][128*32] tf32 hi|lo SWIZZLE_128B tiles of W (row = vertex, K = joint, padded to 32)
   float* WTimg;        // [NP/96][2][32*32] tf32 hi|lo tiles of [W | 1]^T (row = joint, K = vertex)  (skin_bwdA_tc.cu)
@@ -70,7 +74,7 @@ struct uuo_ws {
   float* A;       // [F][J][12]   rows of [R | t]   (lbs.py:403-405 relative transforms, 3x4 part)
   float* vposed;  // [F][NP]
   float* gvposed; // [F][NP]
-  float* gA;      // [<= 2*NSPLIT_GA][F][GA_STRIDE]
+  float* gA;      // [<= 2*NSPLIT_GA + 1][F][GA_STRIDE]  (+1: the extra-joint slab)
   float* gcoef;   // [NSPLIT_GC][F][KP]
   float* gbetas;  // [F][16]
   float* rowbuf;  // [F][R<=64][4]  scratch of the row-sparse paths
@@ -91,7 +95,7 @@ static inline uuo_ws carve_ws(const uuo_model* m, int F, void* base) {
   w.A = take((size_t)F * m->J * 12);
   w.vposed = take((size_t)F * m->NP);
   w.gvposed = take((size_t)F * m->NP);
-  w.gA = take((size_t)2 * UUO_NSPLIT_GA * F * UUO_GA_STRIDE);   // tensor-core path: hi and lo slab per vertex split
+  w.gA = take((size_t)(2 * UUO_NSPLIT_GA + 1) * F * UUO_GA_STRIDE);   // tensor-core path: hi and lo slab per vertex split
   w.gcoef = take((size_t)UUO_NSPLIT_GC * F * m->KP);
   w.gbetas = take((size_t)F * 16);
   w.rowbuf = take((size_t)F * 64 * 4);
@@ -158,7 +162,7 @@ int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const f
 int launch_skin_bwdA_tc(const uuo_model* m, int F, const float* g_vertices, const float* g_joints, const uuo_ws& ws,
                         cudaStream_t st);
 int uuo_bwdA_splits(const uuo_model* m);
-int uuo_ga_parts(const uuo_model* m);
+int uuo_ga_parts(const uuo_model* m, bool with_g_joints);
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st);
 int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, const float* g_joints,

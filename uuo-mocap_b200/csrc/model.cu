@@ -138,7 +138,25 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   std::vector<int32_t> ex(std::max(NE, 1), 0);
   for (int e = 0; e < NE; ++e) { ex[e] = extra_joint_ids[e]; vflag[ex[e]] = 1; }
 
+  // distinct vertices among the extra joints (CSR), for the extra-joint backward kernels
+  std::vector<int32_t> xu_vert, xu_start(1, 0), xu_list;
+  for (int e = 0; e < NE; ++e) {
+    bool seen = false;
+    for (int q = 0; q < e; ++q) seen |= ex[q] == ex[e];
+    if (seen) continue;
+    xu_vert.push_back(ex[e]);
+    for (int q = e; q < NE; ++q)
+      if (ex[q] == ex[e]) xu_list.push_back(q);
+    xu_start.push_back((int32_t)xu_list.size());
+  }
+  m->NU = (int)xu_vert.size();
+  if (xu_vert.empty()) { xu_vert.push_back(0); xu_list.push_back(0); }
+
   int rc = UUO_OK;
+  if ((rc = upload(&m->xu_vert, xu_vert)) || (rc = upload(&m->xu_start, xu_start)) || (rc = upload(&m->xu_list, xu_list))) {
+    uuo_model_destroy(m);
+    return rc;
+  }
   if ((rc = upload(&m->vt, vt)) || (rc = upload(&m->Bmat, Bmat)) || (rc = upload(&m->Bt, Bt)) ||
       (rc = upload(&m->J0, J0)) || (rc = upload(&m->Jdirs, Jdirs)) || (rc = upload(&m->W, W)) ||
       (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
@@ -156,7 +174,7 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
   if (!m) return;
   cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
   cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
-  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg); cudaFree(m->WTimg);
+  cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg); cudaFree(m->WTimg); cudaFree(m->xu_vert); cudaFree(m->xu_start); cudaFree(m->xu_list);
   delete m;
 }
 

@@ -15,7 +15,10 @@ static bool skin_simt() {
 }
 
 // number of d(A) partial slabs launch_skin_backward writes to ws.gA
-int uuo_ga_parts(const uuo_model* m) { return skin_simt() ? UUO_NSPLIT_GA : 2 * uuo_bwdA_splits(m); }
+int uuo_ga_parts(const uuo_model* m, bool with_g_joints) {
+  if (skin_simt()) return UUO_NSPLIT_GA;
+  return 2 * uuo_bwdA_splits(m) + ((with_g_joints && m->NE > 0) ? 1 : 0);
+}
 
 #define SK_THREADS 128
 #define SK_VPT 2
@@ -271,6 +274,68 @@ __global__ void __launch_bounds__(GA_THREADS) skin_backward_A_kernel(
   }
 }
 
+// ---- extra-joint rows of g_joints (vertex_joint_selector.py:73-80): joints[J+e] = vertices[extra_ids[e]], so their
+// upstream gradient lands on NU <= NE distinct vertices.  The tensor-core kernels see g_vertices only; these two tiny
+// kernels add the remaining rank-NU terms: g_vposed[f, v_u] += R(f,v_u)^T gj_u and one more dA slab.
+__global__ void extras_vposed_kernel(const float* __restrict__ W, const float* __restrict__ A,
+                                     const float* __restrict__ g_joints, const int32_t* __restrict__ xu_vert,
+                                     const int32_t* __restrict__ xu_start, const int32_t* __restrict__ xu_list, int F,
+                                     int NU, int J, int NE, int NP, float* __restrict__ gvposed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F * NU) return;
+  const int f = i / NU, u = i % NU, v = xu_vert[u];
+  float gj[3] = {0.f, 0.f, 0.f};
+  for (int q = xu_start[u]; q < xu_start[u + 1]; ++q) {
+    const float* p = g_joints + ((size_t)f * (J + NE) + J + xu_list[q]) * 3;
+    gj[0] += p[0]; gj[1] += p[1]; gj[2] += p[2];
+  }
+  float R[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int j = 0; j < J; ++j) {
+    const float w = W[(size_t)v * J + j];
+    const float* a = A + ((size_t)f * J + j) * 12;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) R[r * 3 + c] = fmaf(w, a[r * 4 + c], R[r * 3 + c]);
+  }
+  float* o = gvposed + (size_t)f * NP + (size_t)v * 3;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) o[c] += R[c] * gj[0] + R[3 + c] * gj[1] + R[6 + c] * gj[2];
+}
+
+__global__ void extras_dA_kernel(const float* __restrict__ W, const float* __restrict__ vposed,
+                                 const float* __restrict__ g_joints, const int32_t* __restrict__ xu_vert,
+                                 const int32_t* __restrict__ xu_start, const int32_t* __restrict__ xu_list, int F, int NU,
+                                 int J, int NE, int NP, float* __restrict__ slab) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F * (J + 1)) return;
+  const int f = i / (J + 1), j = i % (J + 1);
+  float acc[12] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int u = 0; u < NU; ++u) {
+    const int v = xu_vert[u];
+    float gj[3] = {0.f, 0.f, 0.f};
+    for (int q = xu_start[u]; q < xu_start[u + 1]; ++q) {
+      const float* p = g_joints + ((size_t)f * (J + NE) + J + xu_list[q]) * 3;
+      gj[0] += p[0]; gj[1] += p[1]; gj[2] += p[2];
+    }
+    const float w = j < J ? W[(size_t)v * J + j] : 1.f;
+    const float* vp = vposed + (size_t)f * NP + (size_t)v * 3;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const float a = w * gj[r];
+      acc[r * 4] = fmaf(a, vp[0], acc[r * 4]); acc[r * 4 + 1] = fmaf(a, vp[1], acc[r * 4 + 1]);
+      acc[r * 4 + 2] = fmaf(a, vp[2], acc[r * 4 + 2]); acc[r * 4 + 3] += a;
+    }
+  }
+  float* dst = slab + (size_t)f * UUO_GA_STRIDE;
+  if (j < J) {
+#pragma unroll
+    for (int e = 0; e < 12; ++e) dst[j * 12 + e] = acc[e];
+  } else {
+    dst[288] = acc[3]; dst[289] = acc[7]; dst[290] = acc[11]; dst[291] = 0.f;
+  }
+}
+
 int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* vertices, float* joints,
                         const uuo_ws& ws, cudaStream_t st) {
   if (!skin_simt()) {
@@ -301,13 +366,28 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
     int rc;
     ProfScope ps_("skin_backward_vposed", st);
     if ((rc = launch_skin_tc(m, 1, F, g_vertices, g_joints, nullptr, ws.gvposed, ws, st))) return rc;
+    if (g_joints && m->NE > 0) {
+      const int n = F * m->NU;
+      extras_vposed_kernel<<<(n + 127) / 128, 128, 0, st>>>(m->W, ws.A, g_joints, m->xu_vert, m->xu_start, m->xu_list, F,
+                                                            m->NU, m->J, m->NE, m->NP, ws.gvposed);
+      UUO_LAUNCH_CHECK();
+    }
   } else { ProfScope ps_("skin_backward_vposed", st);
   skin_backward_vposed_kernel<<<grid1, SK_THREADS, 0, st>>>(m->W, ws.A, g_vertices, g_joints, m->extra_ids, m->vflag,
                                                             F, m->V, m->NE, m->NP, ws.gvposed);
   } UUO_LAUNCH_CHECK();
   if (!skin_simt()) {
     ProfScope ps_("skin_backward_A", st);
-    return launch_skin_bwdA_tc(m, F, g_vertices, g_joints, ws, st);
+    int rc = launch_skin_bwdA_tc(m, F, g_vertices, g_joints, ws, st);
+    if (rc) return rc;
+    if (g_joints && m->NE > 0) {
+      const int n = F * (m->J + 1);
+      float* slab = ws.gA + (size_t)2 * uuo_bwdA_splits(m) * F * UUO_GA_STRIDE;
+      extras_dA_kernel<<<(n + 127) / 128, 128, 0, st>>>(m->W, ws.vposed, g_joints, m->xu_vert, m->xu_start, m->xu_list, F,
+                                                        m->NU, m->J, m->NE, m->NP, slab);
+      UUO_LAUNCH_CHECK();
+    }
+    return UUO_OK;
   }
   const int vps = ((m->V + UUO_NSPLIT_GA - 1) / UUO_NSPLIT_GA + GA_VC - 1) / GA_VC * GA_VC;
   dim3 grid2((F + GA_FB - 1) / GA_FB, UUO_NSPLIT_GA);

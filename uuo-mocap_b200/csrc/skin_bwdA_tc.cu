@@ -1,6 +1,7 @@
 // d(A) of linear blend skinning on the tensor cores:
 //   dA[f,j,(r,c)] = sum_v W[v,j] g[f,v,r] [v_posed[f,v]; 1][c]        (adjoint of lbs.py:237-250)
 //   dtransl-like row  gsum[f,r] = sum_v g[f,v,r]                      (a 25th all-ones "joint" row)
+// with g = g_vertices (the extra-joint rows of g_joints are added by extras_backward, skin.cu, as one more slab)
 // as the GEMM  D[j, (f,e)] = W'[j, v] . Q[(f,e), v]^T  contracted over the vertices (K, blocks of 32):
 //   A operand (M = 64): rows 0..31 = tf32 hi of [W | 1 | 0]^T, rows 32..63 = its lo part (one constant 8 KB image per
 //   K block, bulk-copied);  B operand (N = 240 = 20 frames x 12 entries): Q = g (x) [v_posed;1], which never exists in
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
     // ===== Q producers: group = stage; a thread owns (frame fl, 4 consecutive vertices) of its group's K blocks =====
     const int pw = warp - WARP_PROD0, grp = pw / GROUP_WARPS, wg = pw % GROUP_WARPS;
     const int fl = wg * 4 + (lane >> 3), c4 = lane & 7;
-    const bool g_vec2 = (a.V & 1) == 0;   // rows of g_vertices are 8 B aligned -> float2 loads
+    const bool g_vec2 = (a.V & 1) == 0 && (reinterpret_cast<uintptr_t>(a.g_vertices) & 7) == 0;   // 8 B aligned rows -> float2 loads
     // position of a K block in this CTA's sequence: (item index, block within the split), advanced STAGES at a time
     struct Pos { int item, kl, f, v0; bool live; };
     auto resolve = [&](Pos& q) {
@@ -124,18 +125,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
             if (i < nvalid) gg[i] = __ldg(gp + i);
         }
       }
-      if (a.g_joints) ff = __ldg(reinterpret_cast<const uint32_t*>(a.vflag + q.v0));   // consumed after the wait
-    };
-    // rare: vertices that are also extra joints receive the g_joints rows (vertex_joint_selector.py:73-80)
-    auto add_extras = [&](const Pos& q, float (&gg)[12], uint32_t ff) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if ((ff >> (8 * i)) & 0xff)
-          for (int e = 0; e < a.NE; ++e)
-            if (a.extra_ids[e] == q.v0 + i) {
-              const float* t = a.g_joints + ((size_t)q.f * (a.J + a.NE) + a.J + e) * 3;
-              gg[i * 3] += t[0]; gg[i * 3 + 1] += t[1]; gg[i * 3 + 2] += t[2];
-            }
     };
     float g[12], p[12], gn[12], pn[12];
     uint32_t vf = 0u, vfn = 0u;
@@ -148,7 +137,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
       advance(nxt);
       load(nxt, gn, pn, vfn);
       umma::mbar_wait(EMPTY(grp), (n & 1) ^ 1);
-      if (vf) add_extras(cur, g, vf);
       uint8_t* q_hi = sm + grp * STAGE_BYTES;
       uint8_t* q_lo = q_hi + Q_BYTES;
 #pragma unroll

@@ -4,7 +4,7 @@
 // entries = 192 columns, K = 24 (three kind::tf32 k-steps), 3xTF32 split for fp32 accuracy.  The epilogue thread of
 // lane v reads its 12 blended entries per frame straight from TMEM and applies them:
 //   mode 0 (forward)      vertices[f,v] = T[:, :3] v_posed[f,v] + T[:, 3] + transl[f]
-//   mode 1 (d v_posed)    g_vposed[f,v] = T[:, :3]^T g[f,v]            (g = g_vertices + extra-joint rows of g_joints)
+//   mode 1 (d v_posed)    g_vposed[f,v] = T[:, :3]^T g_vertices[f,v]   (extra-joint rows of g_joints: extras_backward, skin.cu)
 // Operands: W is a model constant (pre-split, pre-swizzled image, resident in smem for the whole CTA); the transforms
 // are packed once per call into the same image format by pack_transforms_kernel and fetched with one 48 KB bulk copy
 // per frame tile.  Accumulators are double buffered in TMEM so MMAs of tile i+1 overlap the epilogue of tile i.
@@ -20,11 +20,15 @@ constexpr int NF = 16;                  // frames per tile
 constexpr int NCOL = NF * 12;           // 192 accumulator columns (MMA N)
 constexpr int W_BYTES = VT * 128;       // 16 KB per half (hi / lo)
 constexpr int T_BYTES = NCOL * 128;     // 24 KB per half
-constexpr int STAGES = 3;
+constexpr int T_STAGES = 2;              // transform images (bulk copy -> MMA)
+constexpr int X_STAGES = 3;              // per-vertex inputs of a tile (cp.async -> epilogue)
+constexpr int XROW = 400;                 // smem slot of one input row: 384 B + up to 12 B alignment shift
+constexpr int XW_BYTES = 8 * XROW + 128;  // per warp and stage: 8 frame rows (+ 8 transl rows)
+constexpr int X_BYTES = 8 * XW_BYTES;     // all epilogue warps
 constexpr int EPI_WARPS = 8;
 constexpr int WARP_MMA = EPI_WARPS, WARP_LOAD = EPI_WARPS + 1;
 constexpr int NTHREADS = (EPI_WARPS + 2) * 32;   // 320
-constexpr int SMEM_BYTES = 1024 + 2 * W_BYTES + STAGES * 2 * T_BYTES + 256;
+constexpr int SMEM_BYTES = 1024 + 2 * W_BYTES + T_STAGES * 2 * T_BYTES + X_STAGES * X_BYTES + 256;
 
 // Aimg[ft][half][row = fl*12 + e][32] (SWIZZLE_128B), element k = joint
 __global__ void pack_transforms_kernel(const float* __restrict__ A, int F, int n_ftiles, float* __restrict__ Aimg) {
@@ -64,23 +68,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
   const uint32_t raw = umma::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* sm = smem_raw + (base - raw);
-  const uint32_t w_smem = base, t_smem = base + 2 * W_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + 2 * W_BYTES + STAGES * 2 * T_BYTES);
-  // bars: [0,S) full, [S,2S) empty, [2S,2S+2) tmem_full, [2S+2,2S+4) tmem_empty, [2S+4] W loaded
+  const uint32_t w_smem = base, t_smem = base + 2 * W_BYTES, x_smem = t_smem + T_STAGES * 2 * T_BYTES;
+  uint8_t* x_ptr = sm + 2 * W_BYTES + T_STAGES * 2 * T_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(x_ptr + X_STAGES * X_BYTES);
   const uint32_t bar0 = umma::smem_u32(bars);
-  auto FULL = [&](int s) { return bar0 + 8u * s; };
-  auto EMPTY = [&](int s) { return bar0 + 8u * (STAGES + s); };
-  auto TFULL = [&](int q) { return bar0 + 8u * (2 * STAGES + q); };
-  auto TEMPTY = [&](int q) { return bar0 + 8u * (2 * STAGES + 2 + q); };
-  const uint32_t WBAR = bar0 + 8u * (2 * STAGES + 4);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 5);
+  // transform ring (bulk copy -> MMA), input ring (cp.async -> epilogue), accumulator ring (MMA -> epilogue)
+  auto TF_FULL = [&](int s) { return bar0 + 8u * s; };
+  auto TF_EMPTY = [&](int s) { return bar0 + 8u * (T_STAGES + s); };
+  auto X_FULL = [&](int s) { return bar0 + 8u * (2 * T_STAGES + s); };
+  auto X_EMPTY = [&](int s) { return bar0 + 8u * (2 * T_STAGES + X_STAGES + s); };
+  auto TFULL = [&](int q) { return bar0 + 8u * (2 * T_STAGES + 2 * X_STAGES + q); };
+  auto TEMPTY = [&](int q) { return bar0 + 8u * (2 * T_STAGES + 2 * X_STAGES + 2 + q); };
+  const uint32_t WBAR = bar0 + 8u * (2 * T_STAGES + 2 * X_STAGES + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * T_STAGES + 2 * X_STAGES + 5);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int vt = blockIdx.x;
   const int ft0 = blockIdx.y * a.ft_per_chunk, ft1 = min(ft0 + a.ft_per_chunk, a.n_ftiles);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { umma::mbar_init(FULL(s), 1); umma::mbar_init(EMPTY(s), 1); }
+    for (int s = 0; s < T_STAGES; ++s) { umma::mbar_init(TF_FULL(s), 1); umma::mbar_init(TF_EMPTY(s), 1); }
     for (int q = 0; q < 2; ++q) { umma::mbar_init(TFULL(q), 1); umma::mbar_init(TEMPTY(q), EPI_WARPS); }
     umma::mbar_init(WBAR, 1);
     umma::fence_barrier_init();
@@ -92,15 +99,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == WARP_LOAD) {
+    // ===== loader: bulk copies of W (once) and of the transform image of every frame tile =====
     if (lane == 0) {
       umma::mbar_arrive_expect_tx(WBAR, 2 * W_BYTES);
       umma::bulk_g2s(w_smem, a.Wimg + (size_t)vt * 2 * VT * 32, 2 * W_BYTES, WBAR);
+    }
+    if (lane == 0) {
       uint32_t it = 0;
       for (int ft = ft0; ft < ft1; ++ft, ++it) {
-        const int s = it % STAGES;
-        umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
-        umma::mbar_arrive_expect_tx(FULL(s), 2 * T_BYTES);
-        umma::bulk_g2s(t_smem + s * 2 * T_BYTES, a.Aimg + (size_t)ft * 2 * NCOL * 32, 2 * T_BYTES, FULL(s));
+        const int ts = it % T_STAGES;
+        umma::mbar_wait(TF_EMPTY(ts), ((it / T_STAGES) & 1) ^ 1);
+        umma::mbar_arrive_expect_tx(TF_FULL(ts), 2 * T_BYTES);
+        umma::bulk_g2s(t_smem + ts * 2 * T_BYTES, a.Aimg + (size_t)ft * 2 * NCOL * 32, 2 * T_BYTES, TF_FULL(ts));
       }
     }
   } else if (warp == WARP_MMA) {
@@ -109,10 +119,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
     umma::mbar_wait(WBAR, 0);
     uint32_t it = 0;
     for (int ft = ft0; ft < ft1; ++ft, ++it) {
-      const int s = it % STAGES;
+      const int s = it % T_STAGES;
       const uint32_t acc = it & 1;
       umma::mbar_wait(TEMPTY(acc), ((it >> 1) & 1) ^ 1);
-      umma::mbar_wait(FULL(s), (it / STAGES) & 1);
+      umma::mbar_wait(TF_FULL(s), (it / T_STAGES) & 1);
       umma::tc_fence_after();
       if (umma::elect_one()) {
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -125,7 +135,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
           umma::mma_tf32(d_tmem, dwl, dth, idesc, 1u);
           umma::mma_tf32(d_tmem, dwh, dtl, idesc, 1u);
         }
-        umma::mma_commit(EMPTY(s));
+        umma::mma_commit(TF_EMPTY(s));
         umma::mma_commit(TFULL(acc));
       }
       __syncwarp();
@@ -133,63 +143,58 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
   } else {
     // ===== epilogue: warp quadrant = TMEM lanes, warp group = which 8 of the tile's 16 frames =====
     const int gq = warp >> 2, quad = warp & 3;
-    const int v = vt * VT + quad * 32 + lane;
+    const int vl = quad * 32 + lane, v = vt * VT + vl;
     const bool v_ok = v < a.V;
-    // extra-joint row of g_joints that aliases this vertex (vertex_joint_selector.py:73-80): first match e0, and a
-    // mask of further matches (none for SMPL, where the 21 extra joints are distinct vertices)
-    int e0 = -1;
-    unsigned long long emore = 0ull;
-    if (MODE == 1 && v_ok && a.g_joints && a.vflag[v])
-      for (int e = 0; e < a.NE && e < 64; ++e)
-        if (a.extra_ids[e] == v) { if (e0 < 0) e0 = e; else emore |= 1ull << e; }
-    // x[i][0..2] = per-frame input of the vertex; x[i][3..5] = transl (mode 0)
-    auto load_x = [&](int ft, float (&x)[8][6]) {
-      const int fbase = ft * NF + gq * 8;
+    // Per-warp input ring: the warp copies exactly the rows it will consume (8 frames x 32 vertices x 12 B = 384 B
+    // contiguous per frame, + the 8 transl rows) with cp.async, X_STAGES - 1 tiles ahead; consumption is warp-local
+    // (cp.async.wait_group + __syncwarp), so no register prefetch sits on the load scoreboard.
+    uint8_t* xw = x_ptr + (size_t)warp * X_STAGES * XW_BYTES;
+    const uint32_t xw_s = x_smem + warp * X_STAGES * XW_BYTES;
+    // A row (frame f, the warp's 32 vertices) is 384 contiguous bytes whose address is only 4/8 B aligned for the
+    // [F][V][3] tensors: copy its 16 B-aligned hull (<= 25 chunks) and remember the shift; slots are 400 B apart.
+    const long pitch = MODE == 0 ? (long)a.NP : (long)a.V * 3;
+    const int v_first = vt * VT + quad * 32;
+    const int row_bytes = MODE == 0 ? 384 : max(0, min(384, (a.V - v_first) * 12));   // bytes of the row that exist
+    const uintptr_t in_base = reinterpret_cast<uintptr_t>(a.in) + (size_t)v_first * 12;
+    const uintptr_t in_end = reinterpret_cast<uintptr_t>(a.in) + (size_t)a.F * pitch * 4;
+    const size_t pitch4 = (size_t)pitch * 4;
+    auto row_shift = [&](int f) { return (uint32_t)((in_base + (size_t)f * pitch * 4) & 15); };
+    auto issue = [&](int ft, int stage) {
+      if (ft < ft1) {
+        const uint32_t dst0 = xw_s + stage * XW_BYTES;
+        const int f0 = ft * NF + gq * 8;
+        const uintptr_t row0 = in_base + (size_t)f0 * pitch4;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int f = fbase + i;
-#pragma unroll
-        for (int c = 0; c < 6; ++c) x[i][c] = 0.f;
-        if (ft < ft1 && f < a.F && v_ok) {
-          if (MODE == 0) {
-            const float* p = a.in + (size_t)f * a.NP + (size_t)v * 3;
-            x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
-            if (a.transl) {
-              const float* t = a.transl + (size_t)f * 3;
-              x[i][3] = __ldg(t); x[i][4] = __ldg(t + 1); x[i][5] = __ldg(t + 2);
-            }
-          } else {
-            if (a.in) {
-              const float* p = a.in + ((size_t)f * a.V + v) * 3;
-              x[i][0] = __ldg(p); x[i][1] = __ldg(p + 1); x[i][2] = __ldg(p + 2);
-            }
-            if (e0 >= 0) {
-              const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e0) * 3;
-              x[i][3] = __ldg(q); x[i][4] = __ldg(q + 1); x[i][5] = __ldg(q + 2);
-            }
+        for (int i = 0; i < 7; ++i) {
+          const int q = lane + 32 * i;
+          if (q < 8 * 25) {
+            const int fi = q / 25, ch = q - fi * 25;
+            const uintptr_t row = row0 + (size_t)fi * pitch4;
+            const uint32_t shift = (uint32_t)(row & 15);
+            const uintptr_t src = row - shift + ch * 16;
+            const bool ok = a.in != nullptr && f0 + fi < a.F && ch * 16 < (int)shift + row_bytes;
+            const uint32_t n = ok ? (uint32_t)min((uintptr_t)16, in_end - src) : 0u;
+            umma::cp_async16(dst0 + fi * XROW + ch * 16, ok ? reinterpret_cast<const void*>(src) : (const void*)a.Wimg, n);
           }
         }
-      }
-      if (MODE == 1 && emore) {   // rare: several extra joints on one vertex
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int f = fbase + i;
-          if (!(ft < ft1 && f < a.F)) continue;
-          for (unsigned long long mk = emore; mk; mk &= mk - 1) {
-            const int e = __ffsll((long long)mk) - 1;
-            const float* q = a.g_joints + ((size_t)f * (a.J + a.NE) + a.J + e) * 3;
-            x[i][3] += q[0]; x[i][4] += q[1]; x[i][5] += q[2];
-          }
+        if (MODE == 0 && lane < 24) {   // transl of the warp's 8 frames, one float per lane (caller memory: 4 B aligned)
+          const long e0 = ((long)ft * NF + gq * 8) * 3 + lane;
+          const bool ok = a.transl != nullptr && e0 < (long)a.F * 3;
+          umma::cp_async4(dst0 + 8 * XROW + lane * 4, ok ? (const void*)(a.transl + e0) : (const void*)a.Wimg, ok ? 4u : 0u);
         }
       }
+      umma::cp_async_commit();
     };
     uint32_t it = 0;
-    float x[8][6], xn[8][6];
-    load_x(ft0, x);
+#pragma unroll
+    for (int d = 0; d < X_STAGES - 1; ++d) issue(ft0 + d, d);
     for (int ft = ft0; ft < ft1; ++ft, ++it) {
       const int fbase = ft * NF + gq * 8;
-      load_x(ft + 1, xn);   // next tile's inputs are in flight while this tile's accumulator is drained
+      issue(ft + X_STAGES - 1, (it + X_STAGES - 1) % X_STAGES);
       const uint32_t acc = it & 1;
+      const float* xin = reinterpret_cast<const float*>(xw + (it % X_STAGES) * XW_BYTES);
+      umma::cp_async_wait<X_STAGES - 1>();
+      __syncwarp();
       umma::mbar_wait(TFULL(acc), (it >> 1) & 1);
       umma::tc_fence_after();
 #pragma unroll
@@ -199,6 +204,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
         umma::tmem_ld16(taddr, r);
         umma::tmem_ld16(taddr + 16, r + 16);
         umma::tmem_ld16(taddr + 32, r + 32);
+        float x[4][3];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {   // lane stride 12 B: conflict-free
+          const int i = st * 4 + k;
+          const float* xr = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(xin) + i * XROW + row_shift(fbase + i)) + lane * 3;
+          x[k][0] = v_ok ? xr[0] : 0.f; x[k][1] = v_ok ? xr[1] : 0.f; x[k][2] = v_ok ? xr[2] : 0.f;
+        }
         umma::tmem_ld_wait();
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -209,15 +221,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
           if (f < a.F) {
             if (MODE == 0) {
               if (v_ok) {
+                const float* tr = xin + 8 * (XROW / 4) + i * 3;   // broadcast read
                 float* o = a.out + ((size_t)f * a.V + v) * 3;
 #pragma unroll
                 for (int rr = 0; rr < 3; ++rr)
-                  o[rr] = (T[rr * 4] * x[i][0] + T[rr * 4 + 1] * x[i][1] + T[rr * 4 + 2] * x[i][2] + T[rr * 4 + 3]) + x[i][3 + rr];
+                  o[rr] = (T[rr * 4] * x[k][0] + T[rr * 4 + 1] * x[k][1] + T[rr * 4 + 2] * x[k][2] + T[rr * 4 + 3]) + tr[rr];
               }
             } else {
               // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads
               float* o = a.out + (size_t)f * a.NP + (size_t)v * 3;
-              const float g0 = x[i][0] + x[i][3], g1 = x[i][1] + x[i][4], g2 = x[i][2] + x[i][5];
+              const float g0 = x[k][0], g1 = x[k][1], g2 = x[k][2];
 #pragma unroll
               for (int c = 0; c < 3; ++c) o[c] = T[c] * g0 + T[4 + c] * g1 + T[8 + c] * g2;
             }
@@ -227,10 +240,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
       umma::tc_fence_before();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(TEMPTY(acc));
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int c = 0; c < 6; ++c) x[i][c] = xn[i][c];
     }
   }
 
