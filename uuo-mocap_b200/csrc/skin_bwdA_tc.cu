@@ -126,16 +126,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
         }
       }
     };
-    float g[12], p[12], gn[12], pn[12];
-    uint32_t vf = 0u, vfn = 0u;
+    // One K block of this group: prefetch the group's next block into (gn, pn), then form Q from (g, p).
+    // The loop below alternates two register sets (no copies), so the loads of the next block stay in flight
+    // across the whole compute phase instead of being waited on at a register move.
     Pos cur{0, grp, 0, 0, false}, nxt;
-    while (cur.kl >= a.kb_per_split) { cur.kl -= a.kb_per_split; ++cur.item; }
-    resolve(cur);
-    load(cur, g, p, vf);
-    for (uint32_t n = 0; cur.live; ++n) {
+    uint32_t n = 0;
+    auto body = [&](float (&g)[12], float (&p)[12], float (&gn)[12], float (&pn)[12]) {
+      uint32_t unused;
       nxt = cur;
       advance(nxt);
-      load(nxt, gn, pn, vfn);
+      load(nxt, gn, pn, unused);
       umma::mbar_wait(EMPTY(grp), (n & 1) ^ 1);
       uint8_t* q_hi = sm + grp * STAGE_BYTES;
       uint8_t* q_lo = q_hi + Q_BYTES;
@@ -161,10 +161,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_bwdA_tc_kernel(const BwdAArg
       umma::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(FULL_Q(grp));
-#pragma unroll
-      for (int i = 0; i < 12; ++i) { g[i] = gn[i]; p[i] = pn[i]; }
-      vf = vfn;
       cur = nxt;
+      ++n;
+    };
+    float gA[12], pA[12], gB[12], pB[12];
+    while (cur.kl >= a.kb_per_split) { cur.kl -= a.kb_per_split; ++cur.item; }
+    resolve(cur);
+    { uint32_t unused; load(cur, gA, pA, unused); }
+    while (cur.live) {
+      body(gA, pA, gB, pB);
+      if (!cur.live) break;
+      body(gB, pB, gA, pA);
     }
   } else if (warp == WARP_LOAD) {
     if (lane == 0) {
