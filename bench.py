@@ -129,6 +129,260 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------
+# fitting-loop workloads (BASELINE.json configs[2] "fit5k", configs[3] "mht", configs[4] "fit100k")
+# ------------------------------------------------------------------------------------------------
+FIT_WORKLOADS = {
+    # name: (description, total frames, hypotheses, scaling, temporal terms)
+    "fit5k": ("configs[2]: video_mocap.yaml fit, 5000 frames per GPU, 41 markers + 4 ghosts, noise 2 mm, dropout 5 %%, "
+              "synthetic video-pose prior", 5000, 1, "weak", False),
+    "mht": ("configs[3]: mht_rotation.yaml, 64 yaw hypotheses x 2000 frames stacked along the frame axis and sharded by "
+            "hypothesis", 2000, 64, "strong", False),
+    "fit100k": ("configs[4]: 100 000-frame capture sharded by frame range, trans_vel + temporal terms on "
+                "(1- and 2-frame halo by P2P send/recv)", 100000, 1, "strong", True),
+}
+
+
+def run_fit(args, rank, world, local, dev):
+    """One step = one closure evaluation + fused Adam update over this rank's frames.  Steps alternate between the
+    two stages of the yaml in equal numbers: K chamfer-stage iterations (full lbs() forward -> correspondence ->
+    row-sparse backward -> priors -> Adam) then K marker-stage iterations (row-sparse forward/backward)."""
+    import uuo_mocap_b200  # noqa: F401
+    from uuo_mocap_b200 import synthetic, ops, fit as fitm
+    from uuo_mocap_b200.dist import Shard, frame_range
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+
+    desc, Ftot, H, scaling, temporal = FIT_WORKLOADS[args.workload]
+    if args.frames:
+        Ftot = args.frames
+    model = synthetic.make_model("top4")
+    smpl = SMPL(_as_struct(model), device=dev)
+    shard = Shard.from_env() if world > 1 else Shard()
+    n_ghost, drop = (0, 0.0) if args.workload == "mht" else (4, 0.05)
+    if scaling == "weak":
+        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=3 + rank, n_ghost=n_ghost, dropout_p=drop,
+                                     noise_std=0.002)
+        lo, hi = 0, Ftot
+        shard_fit = Shard()                 # independent sequences: no cross-rank term
+        frames_global = Ftot * world
+    elif H > 1:
+        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=4, noise_std=0.002)
+        lo, hi = 0, Ftot
+        shard_fit = Shard()                 # hypotheses are independent; sharded by hypothesis below
+        frames_global = Ftot * H
+    else:
+        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=5, n_ghost=n_ghost, dropout_p=drop,
+                                     noise_std=0.002)
+        lo, hi = frame_range(Ftot, rank, world)
+        shard_fit = shard
+        frames_global = Ftot
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[lo:hi]))
+    markers, o_pose, o_betas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas)
+    root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
+    if H > 1:                               # this rank's hypotheses, stacked along the frame axis
+        h0, h1 = frame_range(H, rank, world)
+        Hl = h1 - h0
+        ang = torch.arange(h0, h1, dtype=torch.float32) * (2 * np.pi / H)
+        rep = lambda t: t.repeat((Hl,) + (1,) * (t.dim() - 1)).contiguous()
+        root = (fitm.rot_z(ang.view(Hl, 1, 1, 1)) @ root.unsqueeze(0)).reshape(Hl * Ftot, 1, 3, 3)
+        markers, o_pose, trans = rep(markers), rep(o_pose), rep(trans)
+        groups = Hl
+    else:
+        groups = 1
+    F = markers.shape[0]
+    M = markers.shape[1]
+    prob = fitm.FitProblem(smpl, markers, o_pose, o_betas, shard_fit, groups)
+    betas0 = o_betas.reshape(1, -1).repeat(groups, 1)
+    pb_ch = fitm.ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F), "betas": betas0, "pose_body": o_pose}, dev)
+    pb_mk = fitm.ParamBlock.build({"pose_body": o_pose, "betas": betas0, "root_orient": root, "trans": trans}, dev)
+    root_d = root.to(dev).contiguous()
+    loss_ch = {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0}
+    loss_mk = {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0}
+    if temporal:
+        loss_ch["trans_vel"] = 1.0
+        loss_mk["temporal"] = 1.0
+    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, M).astype(np.int32)).to(dev)
+    state = {k: (torch.zeros_like(pb.flat), torch.zeros_like(pb.flat)) for k, pb in (("ch", pb_ch), ("mk", pb_mk))}
+    it = {"ch": 0, "mk": 0}
+
+    def step(stage):
+        pb = pb_ch if stage == "ch" else pb_mk
+        if stage == "ch":
+            fitm.chamfer_closure(prob, pb, root_d, loss_ch)
+        else:
+            fitm.marker_closure(prob, pb, vidx, loss_mk)
+        it[stage] += 1
+        ops.adam_step(pb.flat, pb.grad, state[stage][0], state[stage][1], 0.01, it[stage])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(stage, n, profile=False):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        if profile:
+            ops.profile_enable(True)
+        e0.record()
+        for _ in range(n):
+            step(stage)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        prof = None
+        if profile:
+            prof = ops.profile_read()
+            ops.profile_enable(False)
+        own = float(t.item())
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), own, prof
+
+    for stage in ("ch", "mk"):
+        for _ in range(args.warmup):
+            step(stage)
+    K = args.steps
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms_ch, own_ch, prof_ch = timed("ch", K, profile=True)
+    ms_mk, own_mk, prof_mk = timed("mk", K, profile=True)
+    value = frames_global * 2 * K / ((ms_ch + ms_mk) * 1e-3)
+
+    # ---- e2e: the reference's stage functions with HOST tensors in and out (optim_chamfer -> compute_nearest_points
+    # -> optim_markers), K Adam iterations per stage, copies inside the timed region
+    cfg = fitm.default_config(num_iters=K, optimizer="adam", lr=0.01)
+    if temporal:
+        cfg["stages"]["chamfer"]["losses"]["trans_vel"] = 1.0
+        cfg["stages"]["marker"]["losses"]["temporal"] = 1.0
+    pin = lambda t: t.clone().pin_memory()
+    h = {"markers": pin(markers), "pose": pin(o_pose), "root": pin(root), "trans": pin(trans), "betas": pin(betas0)}
+    h2d = sum(t.numel() * 4 for t in h.values()) + h["pose"].numel() * 4
+    d2h = sum(h[k].numel() * 4 for k in ("pose", "root", "trans", "betas"))
+
+    def e2e_once():
+        mk = h["markers"].to(dev, non_blocking=True)
+        pose, opose = h["pose"].to(dev, non_blocking=True), h["pose"].to(dev, non_blocking=True)
+        rt, tr, bt = (h[k].to(dev, non_blocking=True) for k in ("root", "trans", "betas"))
+        p = fitm.FitProblem(smpl, mk, opose, o_betas, shard_fit, groups)
+        fitm.optim_chamfer(mk, pose, opose, bt, o_betas, rt, tr, None, None, smpl, cfg, problem=p, groups=groups)
+        if groups == 1:
+            vi = fitm.compute_nearest_points(mk, pose, bt, rt, tr, smpl, config=cfg, shard=shard_fit, as_one_hot=False)
+        else:
+            vi = vidx
+        fitm.optim_markers(mk, pose, opose, bt, o_betas, rt, tr, vi, None, smpl, cfg, problem=p, groups=groups)
+        return [t.to("cpu", non_blocking=False) for t in (pose, rt, tr, bt)]
+
+    e2e_once()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_once()
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = frames_global * 2 * K / float(t.item())
+    clocks = sampler.stop() if sampler else None
+
+    if rank == 0:
+        peaks = _peaks()
+        Vn = V
+        algo = {   # algorithmic bytes (or flops) per launch over this rank's F frames (DESIGN.md section 4)
+            "vposed_gemm": ("tensor", 2.0 * F * KC * 3 * Vn),
+            "skin_forward": ("hbm", F * (2 * 3 * Vn * 4 + J * 48 + 12)),
+            "nn_argmin_tiles": ("hbm", F * (3 * Vn * 4 + M * 12 + M * 8)),
+            "nn_argmin": ("hbm", F * (3 * Vn * 4 + M * 12 + M * 8)),
+            "rows_forward": ("hbm", F * (KC * 4 + J * 48 + M * 12)),
+            "rows_backward": ("hbm", F * (KC * 4 + J * 48 + M * 12 + 292 * 4 + 224 * 4)),
+            "fk_forward": ("hbm", F * (916 + KC * 4 + J * 48 + J * 12)),
+            "fk_backward": ("hbm", F * (2 * 916 + 292 * 4 + 224 * 4)),
+            "adam_step": ("hbm", pb_ch.flat.numel() * 4 * 7),
+        }
+        def dominant(prof, ms):
+            if not prof:
+                return None
+            dom = max(prof.items(), key=lambda kv: kv[1][0])[0]
+            kern = {k: round(v[0] / max(v[1], 1), 4) for k, v in prof.items()}
+            out = {"kernel": dom, "share_of_stage": prof[dom][0] / ms, "ms_per_launch": kern}
+            if dom in algo:
+                bound, work = algo[dom]
+                dur = prof[dom][0] / max(prof[dom][1], 1) * 1e-3
+                if bound == "hbm":
+                    ach, peak, unit = work / dur / 1e9, peaks["hbm"], "GB/s"
+                else:
+                    ach, peak, unit = work / dur / 1e12, peaks["bf16"] / 2.0, "TFLOP/s"
+                out.update({"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
+                            "peak_source": peaks["src"]})
+            return out
+        r_ch, r_mk = dominant(prof_ch, own_ch), dominant(prof_mk, own_mk)
+        roofline = dict(r_ch or {})
+        roofline["traffic"] = None
+        roofline["marker_stage"] = r_mk
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cpu = cpu_closure_rate(args.ref_frames, cap, model)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": 2 * K, "warmup": args.warmup,
+            "ms_per_step": (ms_ch + ms_mk) / (2 * K), "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "frames_this_rank": F, "frames_global": frames_global, "markers": M,
+                       "hypotheses": H, "parallelism": "frame-range shards x%d" % world, "optimizer": "fused Adam",
+                       "l2": "per-iteration working set >= %d MB (vertices) streamed through HBM" % (F * V * 12 // 2**20)},
+            "stages": {"chamfer": {"ms_per_iter": ms_ch / K, "frame_iters_per_sec": frames_global * K / (ms_ch * 1e-3)},
+                       "marker": {"ms_per_iter": ms_mk / K, "frame_iters_per_sec": frames_global * K / (ms_mk * 1e-3)}},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // (2 * K), "d2h_bytes_per_step": d2h // (2 * K),
+                    "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d Adam iterations "
+                            "per stage, one H2D of the capture and one D2H of the fitted parameters per call" % K},
+            "gpu_launches": int(sum(v[1] for v in (prof_ch or {}).values()) + sum(v[1] for v in (prof_mk or {}).values())),
+            "roofline": roofline, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_closure_rate(frames, cap, model):
+    """Oracle chamfer + marker closures (fwd + bwd) + torch Adam on the host cores, `frames` frames."""
+    from oracle import closures
+    from oracle.smpl_oracle import OracleSMPL
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    orc = OracleSMPL.from_model(model)
+    sl = slice(0, frames)
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[sl]))
+    mk, opose, obetas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas)
+    root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
+    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, mk.shape[1]).astype(np.int64))
+    res = {}
+    for stage in ("chamfer", "marker"):
+        pose = opose.clone().requires_grad_(True)
+        betas = obetas.clone().requires_grad_(True)
+        tr = trans.clone().requires_grad_(True)
+        if stage == "chamfer":
+            z = torch.zeros(frames, 1, 1, requires_grad=True)
+            params = [tr, z, betas, pose]
+            fn = lambda: closures.chamfer_stage_loss(orc, mk, pose, opose, betas, obetas, root, tr, z,
+                                                     {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0})
+        else:
+            rt = root.clone().requires_grad_(True)
+            params = [pose, betas, rt, tr]
+            fn = lambda: closures.marker_stage_loss(orc, mk, pose, opose, betas, obetas, rt, tr, vidx,
+                                                    {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0})
+        opt = torch.optim.Adam(params, lr=0.01)
+        ts = []
+        for i in range(3):
+            t0 = time.perf_counter()
+            opt.zero_grad()
+            fn().backward()
+            opt.step()
+            ts.append(time.perf_counter() - t0)
+        res[stage + "_s"] = float(np.median(ts[1:]))
+    return {"value": 2 * frames / (res["chamfer_s"] + res["marker_s"]), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d frames, chamfer + marker closure (fwd+bwd) + Adam, median of 2 after 1 warm-up, torch threads=%d"
+                      % (frames, threads),
+            "chamfer_s": res["chamfer_s"], "marker_s": res["marker_s"]}
+
+
 WORKLOAD = "configs[1]: SMPL lbs() forward+backward microbench, %d frames per GPU, synthetic SMPL-shaped model (dense-24 weights)"
 
 
@@ -137,7 +391,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--frames", type=int, default=4096, help="frames per GPU")
+    ap.add_argument("--frames", type=int, default=0, help="frames per GPU (lbs: default 4096; fit workloads: their own)")
+    ap.add_argument("--workload", default="lbs", choices=["lbs"] + sorted(FIT_WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-frames", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -148,6 +403,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
+        args.frames = args.frames or 4096
         run_reference(args, rank, world)
         return
 
@@ -158,6 +414,13 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+
+    if args.workload != "lbs":
+        if args.steps == 200:
+            args.steps = 50
+        run_fit(args, rank, world, local, dev)
+        return
+    args.frames = args.frames or 4096
 
     import uuo_mocap_b200  # noqa: F401
     from uuo_mocap_b200 import synthetic, ops, _lib

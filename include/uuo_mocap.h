@@ -104,6 +104,17 @@ int uuo_lbs_forward_rows(const uuo_model* m, const float* betas, int betas_rows,
 int uuo_nn_argmin(const float* markers, const float* vertices, int F, int M, int V, float* dist2,
                   int32_t* idx, void* stream);
 
+/* Same outputs as uuo_nn_argmin, bit for bit, without scanning every vertex: `order[V]` (device) is a
+ * permutation of the vertex ids in which consecutive entries are spatially close (uuo_model_vertex_order
+ * returns the model's: dominant joint, then Morton code of the template).  Tiles of 32 consecutive entries
+ * are bounded per frame by their axis-aligned box; a tile is evaluated only when the distance to its box,
+ * computed with the exact distance's own fp32 operation sequence (monotone rounding => a true lower
+ * bound), does not exceed the best distance so far.  order == NULL falls back to uuo_nn_argmin. */
+int uuo_nn_argmin_ordered(const float* markers, const float* vertices, const int32_t* order, int F, int M,
+                          int V, float* dist2, int32_t* idx, void* stream);
+/* device pointer owned by the model, [V] int32 */
+const int32_t* uuo_model_vertex_order(const uuo_model* m);
+
 /* get_marker_mask (optimization.py:703-715): mask[F,M] = (|x|+|y|+|z| != 0) as float 0/1. */
 int uuo_marker_mask(const float* markers, int n_markers_total, float* mask, void* stream);
 

@@ -39,6 +39,7 @@ struct uuo_model {
   int32_t* xu_vert;    // [NU]   the vertex
   int32_t* xu_start;   // [NU+1] CSR into xu_list
   int32_t* xu_list;    // [NE]   extra-joint indices e aliasing that vertex
+  int32_t* vorder;     // [V]    spatially coherent vertex permutation (nn_tiles.cu)
   float* Bimg_fwd;     // [NP/256][KP/32][2][256*32] tf32 hi|lo SWIZZLE_128B tiles of Bt   (umma_gemm.cu)
   float* Wimg;         // [NP/384][2][128*32] tf32 hi|lo SWIZZLE_128B tiles of W (row = vertex, K = joint, padded to 32)
   float* WTimg;        // [NP/96][2][32*32] tf32 hi|lo tiles of [W | 1]^T (row = joint, K = vertex)  (skin_bwdA_tc.cu)

@@ -189,6 +189,7 @@ extern "C" int uuo_chamfer_rows(const float* markers, const float* vertices, con
                                 int F, int M, int V, float scale, float* loss_sum, float* g_rows, void* stream) {
   UUO_CHECK_ARG(markers && vertices && idx, "NULL pointer");
   if (F * M == 0) return UUO_OK;
+  ProfScope ps_("chamfer_rows", (cudaStream_t)stream);
   chamfer_rows_kernel<<<(F * M + 255) / 256, 256, 0, (cudaStream_t)stream>>>(markers, vertices, mask, idx, F, M, V,
                                                                              scale, loss_sum, g_rows);
   UUO_LAUNCH_CHECK();
@@ -199,6 +200,7 @@ extern "C" int uuo_marker_loss_rows(const float* markers, const float* virt, con
                                     float scale, float* loss_sum, float* g_virt, void* stream) {
   UUO_CHECK_ARG(markers && virt, "NULL pointer");
   if (n == 0) return UUO_OK;
+  ProfScope ps_("marker_loss_rows", (cudaStream_t)stream);
   marker_loss_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(markers, virt, mask, n, dist, scale, loss_sum,
                                                                         g_virt);
   UUO_LAUNCH_CHECK();
@@ -209,6 +211,7 @@ extern "C" int uuo_sqdiff_accumulate(const float* x, const float* y, size_t n, f
                                      float* g, void* stream) {
   UUO_CHECK_ARG(x && y, "NULL pointer");
   if (n == 0) return UUO_OK;
+  ProfScope ps_("sqdiff", (cudaStream_t)stream);
   sqdiff_kernel<<<nblocks(n), 256, 0, (cudaStream_t)stream>>>(x, y, n, scale, loss_sum, g);
   UUO_LAUNCH_CHECK();
   return UUO_OK;
@@ -219,6 +222,7 @@ extern "C" int uuo_temporal_accumulate(const float* x, const float* prev2, const
   UUO_CHECK_ARG(x && F >= 0 && D > 0, "bad arguments");
   if (F == 0) return UUO_OK;
   size_t n = (size_t)F * D;
+  ProfScope ps_("temporal", (cudaStream_t)stream);
   temporal_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, prev2, next2, F, D, scale,
                                                                                  loss_sum, g);
   UUO_LAUNCH_CHECK();
@@ -237,6 +241,7 @@ extern "C" int uuo_transvel_accumulate(const float* trans, const float* mm, cons
                                        int F, float scale, float* loss_sum, float* g_trans, void* stream) {
   UUO_CHECK_ARG(trans && mm, "NULL pointer");
   if (F == 0) return UUO_OK;
+  ProfScope ps_("transvel", (cudaStream_t)stream);
   transvel_kernel<<<(F * 3 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(trans, mm, prev, next, F, scale, loss_sum,
                                                                          g_trans);
   UUO_LAUNCH_CHECK();
@@ -249,6 +254,7 @@ extern "C" int uuo_adam_step(float* param, const float* grad, float* exp_avg, fl
   if (n == 0) return UUO_OK;
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  ProfScope ps_("adam_step", (cudaStream_t)stream);
   adam_kernel<<<nblocks(n), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, beta1, beta2, eps,
                                                             (float)((double)lr / bc1), (float)sqrt(bc2));
   UUO_LAUNCH_CHECK();

@@ -134,6 +134,36 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
   }
   uuo_build_b_image(img_wt, WT.data(), 32, NP / 3, 32);
 
+  // spatially coherent visiting order for the pruned correspondence kernel (nn_tiles.cu): leaves of a balanced
+  // kd-tree over the template -- split the longest axis so that the left part holds a multiple of 32 vertices;
+  // consecutive leaves (tiles of 32) share ancestors, so 32 consecutive tiles are a coherent region as well
+  std::vector<int32_t> vorder(V);
+  {
+    for (int v = 0; v < V; ++v) vorder[v] = v;
+    std::vector<std::pair<int, int>> stack(1, std::make_pair(0, V));
+    while (!stack.empty()) {
+      const int b0 = stack.back().first, e0 = stack.back().second;
+      stack.pop_back();
+      const int n = e0 - b0;
+      if (n <= 32) continue;
+      float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+      for (int i = b0; i < e0; ++i)
+        for (int k = 0; k < 3; ++k) {
+          const float x = v_template[vorder[i] * 3 + k];
+          lo[k] = std::min(lo[k], x); hi[k] = std::max(hi[k], x);
+        }
+      int ax = 0;
+      for (int k = 1; k < 3; ++k)
+        if (hi[k] - lo[k] > hi[ax] - lo[ax]) ax = k;
+      const int mid = b0 + 32 * (((n + 31) / 32) / 2);
+      std::stable_sort(vorder.begin() + b0, vorder.begin() + e0, [&](int32_t a, int32_t c) {
+        return v_template[a * 3 + ax] < v_template[c * 3 + ax];
+      });
+      stack.push_back(std::make_pair(b0, mid));
+      stack.push_back(std::make_pair(mid, e0));
+    }
+  }
+
   std::vector<uint8_t> vflag(NP / 3, 0);   // padded: read 4 flags at a time
   std::vector<int32_t> ex(std::max(NE, 1), 0);
   for (int e = 0; e < NE; ++e) { ex[e] = extra_joint_ids[e]; vflag[ex[e]] = 1; }
@@ -162,7 +192,7 @@ extern "C" int uuo_model_create(const float* v_template, const float* shapedirs,
       (rc = upload(&m->ell_j, ell_j)) || (rc = upload(&m->ell_w, ell_w)) ||
       (rc = upload(&m->extra_ids, ex)) || (rc = upload(&m->vflag, vflag)) ||
       (rc = upload(&m->Bimg_fwd, img_fwd)) || (rc = upload(&m->Bimg_bwd, img_bwd)) ||
-      (rc = upload(&m->Wimg, img_w)) || (rc = upload(&m->WTimg, img_wt))) {
+      (rc = upload(&m->Wimg, img_w)) || (rc = upload(&m->WTimg, img_wt)) || (rc = upload(&m->vorder, vorder))) {
     uuo_model_destroy(m);
     return rc;
   }
@@ -175,8 +205,11 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
   cudaFree(m->vt); cudaFree(m->Bmat); cudaFree(m->Bt); cudaFree(m->J0); cudaFree(m->Jdirs);
   cudaFree(m->W); cudaFree(m->ell_j); cudaFree(m->ell_w); cudaFree(m->extra_ids); cudaFree(m->vflag);
   cudaFree(m->Bimg_fwd); cudaFree(m->Bimg_bwd); cudaFree(m->Wimg); cudaFree(m->WTimg); cudaFree(m->xu_vert); cudaFree(m->xu_start); cudaFree(m->xu_list);
+  cudaFree(m->vorder);
   delete m;
 }
+
+extern "C" const int32_t* uuo_model_vertex_order(const uuo_model* m) { return m ? m->vorder : nullptr; }
 
 extern "C" int uuo_model_info(const uuo_model* m, int what) {
   if (!m) return UUO_ERR_ARG;

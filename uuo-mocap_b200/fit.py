@@ -158,8 +158,8 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
         verts = prob.lbs_forward(brows, root_orient, v["pose_body"], v["z_angle"], v["trans"])
         w_ch = float(losses.get("full_chamfer", 0.0))
         if w_ch != 0.0 and prob.wsum_global > 0:
-            check(_lib.lib().uuo_nn_argmin(ptr(prob.markers), ptr(verts), F, M, prob.mh.V, ptr(prob.d2), ptr(prob.idx),
-                                           prob._st()))
+            check(_lib.lib().uuo_nn_argmin_ordered(ptr(prob.markers), ptr(verts), prob.mh.vertex_order, F, M, prob.mh.V,
+                                                   ptr(prob.d2), ptr(prob.idx), prob._st()))
             check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.idx), F, M,
                                               prob.mh.V, w_ch / prob.wsum_global, ptr(prob.red[15:]), ptr(prob.g_rows),
                                               prob._st()))
@@ -292,10 +292,10 @@ def get_marker_mask(markers: torch.Tensor) -> torch.Tensor:
 
 
 def weighted_chamfer_distance(x: torch.Tensor, y: torch.Tensor, x_weights: torch.Tensor,
-                              single_directional: bool = False, return_idx: bool = False):
+                              single_directional: bool = False, return_idx: bool = False, model=None):
     """src/video_mocap/losses/chamfer_distance.py:5-21 (always single-directional there): value only, no
     [F*M,V,3] intermediate.  x markers [F,M,3], y vertices [F,V,3], x_weights [F,M]."""
-    d, idx = ops.nn_argmin(x, y)
+    d, idx = ops.nn_argmin(x, y, model)
     w = x_weights.to(d.dtype).reshape(-1)
     s = w.sum()
     val = (d.reshape(-1) * w).sum() / s if float(s) != 0.0 else d.sum() * 0.0

@@ -64,6 +64,8 @@ class ModelHandle:
                                           self.V, self.J, self.NB, self.P, self.NE, self.index, C.byref(h)))
         self.handle = h
         self.max_nnz = _lib.lib().uuo_model_info(h, 6)
+        # device pointer (int32[V]) of the spatially coherent vertex order used by the pruned correspondence kernel
+        self.vertex_order = C.c_void_p(_lib.lib().uuo_model_vertex_order(h))
 
     def __del__(self):
         h = getattr(self, "handle", None)
