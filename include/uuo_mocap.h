@@ -114,6 +114,16 @@ int uuo_nn_argmin_ordered(const float* markers, const float* vertices, const int
                           int V, float* dist2, int32_t* idx, void* stream);
 /* device pointer owned by the model, [V] int32 */
 const int32_t* uuo_model_vertex_order(const uuo_model* m);
+/* the same permutation copied to HOST memory out[V] */
+int uuo_model_vertex_order_host(const uuo_model* m, int32_t* out);
+
+/* Same outputs again for vertices that ALREADY lie in visiting order: the fitting loop evaluates lbs() on a twin
+ * model whose vertices are renumbered by uuo_model_vertex_order, so a tile is 32 consecutive vertices and nothing
+ * is gathered.  ids[V] (device, or NULL = identity) maps a position to the ORIGINAL vertex id: idx[F,M] reports
+ * original ids and ties break on them, exactly like uuo_nn_argmin on the un-permuted vertices; pos[F,M] (may be
+ * NULL) receives the winning position, i.e. the row of `vertices` that holds the matched vertex. */
+int uuo_nn_argmin_presorted(const float* markers, const float* vertices, const int32_t* ids, int F, int M, int V,
+                            float* dist2, int32_t* idx, int32_t* pos, void* stream);
 
 /* get_marker_mask (optimization.py:703-715): mask[F,M] = (|x|+|y|+|z| != 0) as float 0/1. */
 int uuo_marker_mask(const float* markers, int n_markers_total, float* mask, void* stream);

@@ -127,3 +127,61 @@ def test_nn_argmin_model_order_on_posed_bodies(get_model):
     # (read back through a tiny identity trick: argmin of each vertex against itself)
     dd, ii = ops.nn_argmin(verts[:1], verts[:1], model=smpl.handle)
     assert torch.equal(ii[0].cpu().long(), p3d.knn_k1(verts[:1].cpu(), verts[:1].cpu())[1][0])
+
+
+# ---- presorted kernel (vertices already in visiting order; ties break on the ORIGINAL ids) ----
+@pytest.mark.parametrize("F,M,V", [(1, 1, 1), (3, 41, 6890), (5, 45, 6890), (2, 7, 19), (3, 300, 515), (4, 256, 1000),
+                                   (150, 45, 6890)])
+@pytest.mark.parametrize("ties", [False, True])
+@pytest.mark.parametrize("with_ids", [False, True])
+def test_nn_argmin_presorted_bit_exact(F, M, V, ties, with_ids):
+    from uuo_mocap_b200 import ops
+    from oracle import p3d_oracle as p3d
+    m, v = _clouds(F, M, V, seed=F * 1000 + M + 13, ties=ties)
+    if V > 1000:   # make consecutive rows spatially coherent for frame 0 so that tiles are really pruned
+        v = v[:, np.argsort(v[0, :, 0].numpy(), kind="stable")].contiguous()
+    d_ref, i_ref = p3d.knn_k1(m, v)
+    if with_ids:
+        rng = np.random.default_rng(V + 1)
+        perm = rng.permutation(V)                      # row p of the kernel's input is original vertex perm[p]
+        d, i, p = ops.nn_argmin_presorted(m.cuda(), v[:, perm].contiguous().cuda(),
+                                          torch.from_numpy(perm.astype(np.int32)).cuda(), want_pos=True)
+        assert torch.equal(torch.from_numpy(perm)[p.cpu().long()], i.cpu().long())
+    else:
+        d, i, p = ops.nn_argmin_presorted(m.cuda(), v.cuda(), None, want_pos=True)
+        assert torch.equal(p, i)
+    assert torch.equal(i.cpu().long(), i_ref)
+    assert torch.equal(d.cpu(), d_ref)
+
+
+def test_visiting_twin_matches_model(get_model):
+    """The twin's vertices are the model's vertices renumbered; joints identical; presorted NN on the twin ==
+    exhaustive NN on the model (4-byte aligned vertex pointer included)."""
+    from uuo_mocap_b200 import ops, synthetic
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    model = get_model("top4")
+    smpl = SMPL(_as_struct(model), device="cuda:0")
+    twin = smpl.visiting_twin()
+    F = 37
+    cap = synthetic.make_capture(model, F, num_markers=41, seed=12, n_ghost=4, dropout_p=0.1, dropout_block=3,
+                                 noise_std=0.002)
+    rot = torch.from_numpy(synthetic.axis_angle_to_matrix_np(cap.gt_pose_aa.astype(np.float64)).astype(np.float32)).cuda()
+    kw = dict(betas=torch.from_numpy(cap.gt_betas).cuda(), body_pose=rot[:, 1:], global_orient=rot[:, :1],
+              transl=torch.from_numpy(cap.gt_trans).cuda(), pose2rot=False)
+    a, b = smpl(**kw), twin(**kw)
+    ids = twin.visit_ids.long()
+    assert sorted(ids.cpu().tolist()) == list(range(smpl.handle.V))
+    assert float((a.vertices[:, ids] - b.vertices).abs().max()) < 2e-6
+    assert float((a.joints - b.joints).abs().max()) < 2e-6
+    mk = torch.from_numpy(cap.markers).cuda()
+    # feed the SAME numbers to both kernels (the twin's rows mapped back) so the comparison is bit-exact
+    v_orig = torch.empty_like(b.vertices)
+    v_orig[:, ids] = b.vertices
+    d0, i0 = ops.nn_argmin(mk, v_orig)
+    d1, i1, p1 = ops.nn_argmin_presorted(mk, b.vertices.detach(), twin.visit_ids, want_pos=True)
+    assert torch.equal(d0, d1) and torch.equal(i0, i1)
+    assert torch.equal(ids[p1.long()].int(), i1)
+    flat = torch.empty(b.vertices.numel() + 1, device="cuda:0")
+    flat[1:] = b.vertices.detach().reshape(-1)
+    d2, i2 = ops.nn_argmin_presorted(mk, flat[1:].view_as(b.vertices), twin.visit_ids)
+    assert torch.equal(d0, d2) and torch.equal(i0, i2)

@@ -21,19 +21,24 @@ for kind in ("top4", "dense"):
                transl=torch.from_numpy(cap.gt_trans).cuda(), pose2rot=False)
     v = out.vertices.detach().contiguous()
     mk = torch.from_numpy(cap.markers).cuda()
+    twin = smpl.visiting_twin()
+    ids = twin.visit_ids
+    vs = v[:, ids.long()].contiguous()
     res = {}
-    for name, kw in (("exhaustive", {}), ("pruned", {"model": smpl.handle})):
+    for name, kw in (("exhaustive", {}), ("pruned", {"model": smpl.handle}), ("presorted", None)):
+        fn = (lambda: ops.nn_argmin(mk, v, **kw)) if kw is not None else (lambda: ops.nn_argmin_presorted(mk, vs, ids))
         for _ in range(3):
-            d, i = ops.nn_argmin(mk, v, **kw)
+            d, i = fn()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()
         for _ in range(20):
-            d, i = ops.nn_argmin(mk, v, **kw)
+            d, i = fn()
         e1.record()
         torch.cuda.synchronize()
         res[name] = (e0.elapsed_time(e1) / 20, d, i)
-    same = torch.equal(res["exhaustive"][1], res["pruned"][1]) and torch.equal(res["exhaustive"][2], res["pruned"][2])
+    same = all(torch.equal(res["exhaustive"][1], res[k][1]) and torch.equal(res["exhaustive"][2], res[k][2])
+               for k in ("pruned", "presorted"))
     byt = F * (6890 * 12 + 45 * 20)
-    print("%s F=%d: exhaustive %.3f ms, pruned %.3f ms (%.0f GB/s algorithmic), identical=%s"
-          % (kind, F, res["exhaustive"][0], res["pruned"][0], byt / res["pruned"][0] / 1e6, same))
+    print("%s F=%d: exhaustive %.3f ms, pruned (gather) %.3f ms, presorted %.3f ms (%.0f GB/s algorithmic), identical=%s"
+          % (kind, F, res["exhaustive"][0], res["pruned"][0], res["presorted"][0], byt / res["presorted"][0] / 1e6, same))

@@ -31,6 +31,8 @@ SIGNATURES = {
     "uuo_nn_argmin": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "uuo_nn_argmin_ordered": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
     "uuo_model_vertex_order": (_P, [_P]),
+    "uuo_model_vertex_order_host": (_I, [_P, _P]),
+    "uuo_nn_argmin_presorted": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, _P]),
     "uuo_marker_mask": (_I, [_P, _I, _P, _P]),
     "uuo_chamfer_rows": (_I, [_P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
     "uuo_marker_loss_rows": (_I, [_P, _P, _P, _I, _F, _F, _P, _P, _P]),

@@ -211,6 +211,12 @@ extern "C" void uuo_model_destroy(uuo_model* m) {
 
 extern "C" const int32_t* uuo_model_vertex_order(const uuo_model* m) { return m ? m->vorder : nullptr; }
 
+extern "C" int uuo_model_vertex_order_host(const uuo_model* m, int32_t* out) {
+  UUO_CHECK_ARG(m && out, "NULL pointer");
+  UUO_CUDA(cudaMemcpy(out, m->vorder, (size_t)m->V * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  return UUO_OK;
+}
+
 extern "C" int uuo_model_info(const uuo_model* m, int what) {
   if (!m) return UUO_ERR_ARG;
   switch (what) {

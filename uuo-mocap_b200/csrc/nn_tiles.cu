@@ -262,3 +262,252 @@ extern "C" int uuo_nn_argmin_ordered(const float* markers, const float* vertices
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
+
+// =====================================================================================================
+// Presorted variant: the vertices already lie in visiting order (the fitting loop evaluates lbs() on a twin
+// model whose vertices are renumbered by uuo_model_vertex_order), so a tile is 32 CONSECUTIVE vertices and
+// nothing is gathered: the staged frame is read with stride-3 words (conflict-free) straight from the
+// staging buffer.  ids[p] = original vertex id of position p (ties break on the ORIGINAL numbering).
+//   - one persistent CTA per SM, 32 warps; frames double-buffered with 1-D bulk copies (cp.async.bulk ->
+//     mbarrier), so the HBM stream of frame f+1 overlaps all of frame f;
+//   - 3a: one warp per marker finds the closest round, the closest tile in it, evaluates that tile (an
+//     exact distance that bounds everything else) and appends every other (marker, tile) pair whose box
+//     bound does not exceed it to a work list in shared memory;
+//   - 3b: all warps drain the list, one pair per warp at a time (balanced however hard a marker is), merging
+//     with atomicMin on a packed 64-bit key  distance bits | original id | position  -- the lexicographic
+//     minimum the reference's first-minimum scan returns.
+// =====================================================================================================
+#define NP_THREADS 1024
+#define NP_MAXM 256          // markers per pass over a frame
+#define NP_LIST 4096         // (marker, tile) pairs; overflow is evaluated inline by the producing warp
+
+struct np_layout {
+  int nr, ntp, stage_floats;
+  size_t off_box, off_rbox, off_key, off_mk, off_list, total;
+};
+__host__ __device__ inline np_layout np_make_layout(int V) {
+  np_layout L;
+  const int ntiles = (V + 31) / 32;
+  L.nr = (ntiles + 31) / 32;
+  L.ntp = L.nr * 32;
+  L.stage_floats = (3 * V + 8 + 3) & ~3;
+  L.off_box = (size_t)2 * L.stage_floats * 4;
+  L.off_rbox = L.off_box + (size_t)6 * L.ntp * 4;
+  L.off_key = L.off_rbox + 6 * 32 * 4;
+  L.off_mk = L.off_key + NP_MAXM * 8;
+  L.off_list = L.off_mk + NP_MAXM * 3 * 4;
+  L.total = L.off_list + NP_LIST * 4;
+  return L;
+}
+
+__device__ __forceinline__ unsigned long long np_pack(float d, int id, int pos) {
+  return ((unsigned long long)__float_as_uint(d) << 32) | ((unsigned long long)(unsigned)id << 16) | (unsigned)pos;
+}
+
+// evaluate tile t for a marker and merge into key[m]
+__device__ __forceinline__ void np_eval_merge(const float* __restrict__ raw, const int32_t* __restrict__ ids, int V,
+                                              int t, int lane, float mx, float my, float mz,
+                                              unsigned long long* key) {
+  const int pos = min(t * 32 + lane, V - 1);
+  const float* p = raw + 3 * pos;
+  const float d = nt_sqdist(mx, my, mz, p[0], p[1], p[2]);
+  const float dm = redux_min_f32(d);
+  const unsigned cur = (unsigned)(*reinterpret_cast<volatile unsigned long long*>(key) >> 32);
+  // distances are >= 0: their bit patterns order like the values; inf / NaN never win (the exhaustive scan's
+  // strict '<' against an initial +inf never accepts them either)
+  if (__float_as_uint(dm) < 0x7f800000u && __float_as_uint(dm) <= cur) {
+    const int id = ids ? __ldg(ids + pos) : pos;
+    const unsigned cand = d == dm ? (((unsigned)id << 16) | (unsigned)pos) : 0xffffffffu;
+    const unsigned best = __reduce_min_sync(0xffffffffu, cand);
+    if (lane == 0 && best != 0xffffffffu) atomicMin(key, ((unsigned long long)__float_as_uint(dm) << 32) | best);
+  }
+}
+
+__global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float* __restrict__ markers,
+                                                                     const float* __restrict__ vertices,
+                                                                     const int32_t* __restrict__ ids, int F, int M,
+                                                                     int V, float* __restrict__ dist2,
+                                                                     int32_t* __restrict__ idx,
+                                                                     int32_t* __restrict__ pos_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = NP_THREADS, nwarp = NP_THREADS / 32;
+  const np_layout L = np_make_layout(V);
+  const int nr = L.nr, ntp = L.ntp, nflt = 3 * V;
+  float* stage0 = reinterpret_cast<float*>(smem_raw);
+  float* box = reinterpret_cast<float*>(smem_raw + L.off_box);
+  float* rbox = reinterpret_cast<float*>(smem_raw + L.off_rbox);
+  unsigned long long* key = reinterpret_cast<unsigned long long*>(smem_raw + L.off_key);
+  float* mk = reinterpret_cast<float*>(smem_raw + L.off_mk);
+  unsigned* list = reinterpret_cast<unsigned*>(smem_raw + L.off_list);
+  __shared__ __align__(8) uint64_t load_bar[2];
+  __shared__ unsigned list_count;
+  const float INF = __int_as_float(0x7f800000);
+  if (tid == 0) {
+    umma::mbar_init(umma::smem_u32(&load_bar[0]), 1);
+    umma::mbar_init(umma::smem_u32(&load_bar[1]), 1);
+    umma::fence_barrier_init();
+  }
+  __syncthreads();
+  const uintptr_t vbase = reinterpret_cast<uintptr_t>(vertices), vend = vbase + (size_t)F * nflt * 4;
+  auto hull_ok = [&](int f) {
+    const uintptr_t a = vbase + (size_t)f * nflt * 4;
+    return (a & ~(uintptr_t)15) >= vbase && ((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) <= vend;
+  };
+  // stage frame f into buffer b (see nn_tiles_kernel: bulk copy of the 16 B hull, cp.async for out-of-tensor hulls)
+  auto issue_load = [&](int f, int b) {
+    const float* src = vertices + (size_t)f * nflt;
+    float* stage = stage0 + (size_t)b * L.stage_floats;
+    if (hull_ok(f)) {
+      if (tid == 0) {
+        const uint32_t bar = umma::smem_u32(&load_bar[b]);
+        const uintptr_t a = reinterpret_cast<uintptr_t>(src), lo = a & ~(uintptr_t)15;
+        const uint32_t bytes = (uint32_t)(((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) - lo);
+        umma::fence_proxy_async_smem();
+        umma::mbar_arrive_expect_tx(bar, bytes);
+        const uint32_t chunk = ((bytes / 8) + 15) & ~15u;
+        for (uint32_t off = 0; off < bytes; off += chunk)
+          umma::bulk_g2s(umma::smem_u32(stage) + off, reinterpret_cast<const void*>(lo + off), min(chunk, bytes - off), bar);
+      }
+      return;
+    }
+    const int mis = (int)((reinterpret_cast<uintptr_t>(src) & 15) >> 2);
+    float* raw = stage + mis;
+    const int head = min(nflt, (4 - mis) & 3);
+    const int body = (nflt - head) >> 2;
+    const int tail0 = head + 4 * body;
+    if (tid < head) cp_async4(raw + tid, src + tid);
+    for (int i = tid; i < body; i += nthr) cp_async16(raw + head + 4 * i, src + head + 4 * i);
+    if (tid < nflt - tail0) cp_async4(raw + tail0 + tid, src + tail0 + tid);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  uint32_t parity[2] = {0, 0};
+  if ((int)blockIdx.x < F) issue_load(blockIdx.x, 0);
+
+  int buf = 0;
+  for (int f = blockIdx.x; f < F; f += gridDim.x, buf ^= 1) {
+    // the other buffer was last read during the previous frame, which ended with a barrier
+    if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
+    if (hull_ok(f)) { umma::mbar_wait(umma::smem_u32(&load_bar[buf]), parity[buf]); parity[buf] ^= 1; }
+    else if (f + (int)gridDim.x < F && !hull_ok(f + gridDim.x)) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    const float* raw = stage0 + (size_t)buf * L.stage_floats +
+                       (int)((reinterpret_cast<uintptr_t>(vertices + (size_t)f * nflt) & 15) >> 2);
+    // ---- 2. tile boxes: one warp per tile, stride-3 reads (conflict-free)
+    for (int t = warp; t < ntp; t += nwarp) {
+      const float* p = raw + 3 * min(t * 32 + lane, V - 1);     // the tail repeats the last vertex
+      const float x = p[0], y = p[1], z = p[2];
+      const float lx = redux_min_f32(x), ly = redux_min_f32(y), lz = redux_min_f32(z);
+      const float hx = redux_max_f32(x), hy = redux_max_f32(y), hz = redux_max_f32(z);
+      if (lane == 0) {
+        box[t] = lx; box[ntp + t] = ly; box[2 * ntp + t] = lz;
+        box[3 * ntp + t] = hx; box[4 * ntp + t] = hy; box[5 * ntp + t] = hz;
+      }
+    }
+    __syncthreads();
+    for (int r = warp; r < nr; r += nwarp) {
+      const int t = r * 32 + lane;
+      const float lx = redux_min_f32(box[t]), ly = redux_min_f32(box[ntp + t]), lz = redux_min_f32(box[2 * ntp + t]);
+      const float hx = redux_max_f32(box[3 * ntp + t]), hy = redux_max_f32(box[4 * ntp + t]),
+                  hz = redux_max_f32(box[5 * ntp + t]);
+      if (lane == 0) {
+        rbox[r] = lx; rbox[32 + r] = ly; rbox[64 + r] = lz;
+        rbox[96 + r] = hx; rbox[128 + r] = hy; rbox[160 + r] = hz;
+      }
+    }
+    for (int m0 = 0; m0 < M; m0 += NP_MAXM) {
+      const int mc = min(NP_MAXM, M - m0);
+      for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
+      if (tid == 0) list_count = 0;
+      __syncthreads();                                   // round boxes, markers, counter
+      // ---- 3a. bound + candidate pairs, one warp per marker
+      for (int m = warp; m < mc; m += nwarp) {
+        const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
+        const float rlb = lane < nr ? nt_boxdist(rbox, 32, lane, mx, my, mz) : INF;
+        const float rmin = redux_min_f32(rlb);
+        const unsigned bm = __ballot_sync(0xffffffffu, lane < nr && rlb == rmin);
+        const int r0 = bm ? __ffs(bm) - 1 : 0;
+        float lb = nt_boxdist(box, ntp, r0 * 32 + lane, mx, my, mz);
+        const float tmin = redux_min_f32(lb);
+        const unsigned bt = __ballot_sync(0xffffffffu, lb == tmin);
+        const int j0 = bt ? __ffs(bt) - 1 : 0;
+        if (lane == 0) key[m] = np_pack(INF, 0xffff, 0xffff);
+        __syncwarp();
+        np_eval_merge(raw, ids, V, r0 * 32 + j0, lane, mx, my, mz, key + m);
+        __syncwarp();
+        const float best0 = __uint_as_float((unsigned)(*reinterpret_cast<volatile unsigned long long*>(key + m) >> 32));
+        unsigned pend = __ballot_sync(0xffffffffu, lane < nr && !(rlb > best0));     // NaN bounds are never pruned
+        while (pend) {
+          const int r = __ffs(pend) - 1;
+          pend &= pend - 1;
+          lb = nt_boxdist(box, ntp, r * 32 + lane, mx, my, mz);
+          const bool cand = !(lb > best0) && !(r == r0 && lane == j0);
+          const unsigned cb = __ballot_sync(0xffffffffu, cand);
+          if (!cb) continue;
+          const int n = __popc(cb);
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(&list_count, (unsigned)n);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          const unsigned slot = base + __popc(cb & ((1u << lane) - 1u));
+          const bool stored = cand && slot < NP_LIST;
+          if (stored) list[slot] = ((unsigned)m << 16) | (unsigned)(r * 32 + lane);
+          unsigned over = __ballot_sync(0xffffffffu, cand && !stored);           // list full: evaluate here
+          while (over) {
+            const int j = __ffs(over) - 1;
+            over &= over - 1;
+            np_eval_merge(raw, ids, V, r * 32 + j, lane, mx, my, mz, key + m);
+          }
+        }
+      }
+      __syncthreads();
+      // ---- 3b. drain the pair list, one pair per warp at a time
+      const int np = (int)min(list_count, (unsigned)NP_LIST);
+      for (int q = warp; q < np; q += nwarp) {
+        const unsigned e = list[q];
+        const int m = (int)(e >> 16), t = (int)(e & 0xffffu);
+        np_eval_merge(raw, ids, V, t, lane, mk[3 * m], mk[3 * m + 1], mk[3 * m + 2], key + m);
+      }
+      __syncthreads();
+      // ---- 3c. results
+      for (int m = tid; m < mc; m += nthr) {
+        const unsigned long long k = key[m];
+        const unsigned id = (unsigned)(k >> 16) & 0xffffu, ps = (unsigned)k & 0xffffu;
+        const bool none = id == 0xffffu && ps == 0xffffu && (unsigned)(k >> 32) == 0x7f800000u;
+        dist2[(size_t)f * M + m0 + m] = __uint_as_float((unsigned)(k >> 32));
+        idx[(size_t)f * M + m0 + m] = none ? 0 : (int)id;        // all-NaN distances: (inf, 0) like the exhaustive scan
+        if (pos_out) pos_out[(size_t)f * M + m0 + m] = none ? 0 : (int)ps;
+      }
+      if (m0 + NP_MAXM < M) __syncthreads();
+    }
+    __syncthreads();                                     // every warp is done with this frame's buffer
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+extern "C" int uuo_nn_argmin_presorted(const float* markers, const float* vertices, const int32_t* ids, int F, int M,
+                                       int V, float* dist2, int32_t* idx, int32_t* pos, void* stream) {
+  UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
+  UUO_CHECK_ARG(F >= 0 && M >= 0 && V > 0, "bad sizes");
+  const np_layout L = np_make_layout(V);
+  UUO_CHECK_ARG(V < 65535 && L.nr <= 32 && L.total <= 227 * 1024 && M < 65536,
+                "V too large for the presorted correspondence kernel (two staged frames must fit in shared memory)");
+  if (F == 0 || M == 0) return UUO_OK;
+  static thread_local size_t configured = 0;
+  static thread_local int n_sm = 0;
+  if (L.total > configured) {
+    UUO_CUDA(cudaFuncSetAttribute(nn_presorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+    configured = L.total;
+  }
+  if (!n_sm) {
+    int dev = 0;
+    UUO_CUDA(cudaGetDevice(&dev));
+    UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  }
+  {
+    ProfScope ps_("nn_argmin_presorted", (cudaStream_t)stream);
+    nn_presorted_kernel<<<F < n_sm ? F : n_sm, NP_THREADS, L.total, (cudaStream_t)stream>>>(markers, vertices, ids, F, M, V,
+                                                                                          dist2, idx, pos);
+  }
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}

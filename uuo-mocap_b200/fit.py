@@ -60,7 +60,11 @@ class FitProblem:
         self.F_global, self.wsum_global = int(fg[0].item()), float(fg[1].item())
         self.ws = self.mh.workspace(self.F)
         self.vertices = None
+        # dense forward of the chamfer stage runs on the visiting-order twin (rows of `vertices` are renumbered,
+        # see SMPL.visiting_twin); idx holds ORIGINAL vertex ids, pos the matching row of `vertices`
+        self.twin = self.smpl.visiting_twin()
         self.idx = torch.empty((self.F, self.M), dtype=torch.int32, device=dev)
+        self.pos = torch.empty((self.F, self.M), dtype=torch.int32, device=dev)
         self.d2 = torch.empty((self.F, self.M), dtype=torch.float32, device=dev)
         self.g_rows = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
         self.virt = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
@@ -76,8 +80,8 @@ class FitProblem:
     def lbs_forward(self, betas_rows, root, pose, yaw, trans):
         if self.vertices is None:
             self.vertices = torch.empty((self.F, self.mh.V, 3), dtype=torch.float32, device=self.dev)
-        check(_lib.lib().uuo_lbs_forward(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
-                                         POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(self.vertices), None,
+        check(_lib.lib().uuo_lbs_forward(self.twin.handle.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root),
+                                         ptr(pose), POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(self.vertices), None,
                                          ptr(self.ws), self._st()))
         return self.vertices
 
@@ -158,14 +162,15 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
         verts = prob.lbs_forward(brows, root_orient, v["pose_body"], v["z_angle"], v["trans"])
         w_ch = float(losses.get("full_chamfer", 0.0))
         if w_ch != 0.0 and prob.wsum_global > 0:
-            check(_lib.lib().uuo_nn_argmin_ordered(ptr(prob.markers), ptr(verts), prob.mh.vertex_order, F, M, prob.mh.V,
-                                                   ptr(prob.d2), ptr(prob.idx), prob._st()))
-            check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.idx), F, M,
+            check(_lib.lib().uuo_nn_argmin_presorted(ptr(prob.markers), ptr(verts), ptr(prob.twin.visit_ids), F, M,
+                                                     prob.mh.V, ptr(prob.d2), ptr(prob.idx), ptr(prob.pos), prob._st()))
+            check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.pos), F, M,
                                               prob.mh.V, w_ch / prob.wsum_global, ptr(prob.red[15:]), ptr(prob.g_rows),
                                               prob._st()))
         else:
             prob.g_rows.zero_()
             prob.idx.zero_()
+            prob.pos.zero_()
         prob.lbs_backward_rows(brows, root_orient, v["pose_body"], v["z_angle"], prob.idx, False, prob.g_rows,
                                prob.gbetas_target(), None, g["pose_body"], g["z_angle"], g["trans"])
         if "reg_pose_body" in losses:                                                   # :243-245

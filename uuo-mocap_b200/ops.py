@@ -52,6 +52,27 @@ def nn_argmin(markers: torch.Tensor, vertices: torch.Tensor, model=None,
     return d, i
 
 
+def nn_argmin_presorted(markers: torch.Tensor, vertices: torch.Tensor, ids: Optional[torch.Tensor] = None,
+                        want_pos: bool = False):
+    """uuo_nn_argmin_presorted: ``vertices`` [F,V,3] already lie in visiting order (a twin model's output),
+    ``ids`` [V] int32 gives the original id of every row.  Returns (dist2, idx) or (dist2, idx, pos)."""
+    markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
+    F, M, _ = markers.shape
+    V = vertices.shape[1]
+    if vertices.shape[0] != F:
+        raise ValueError("markers and vertices must have the same number of frames")
+    if ids is not None and not (ids.is_cuda and ids.dtype == torch.int32 and ids.numel() == V and ids.is_contiguous()):
+        raise ValueError("ids must be a contiguous int32 CUDA tensor with V entries")
+    dev = markers.device
+    d = torch.empty((F, M), dtype=torch.float32, device=dev)
+    i = torch.empty((F, M), dtype=torch.int32, device=dev)
+    p = torch.empty((F, M), dtype=torch.int32, device=dev) if want_pos else None
+    with torch.cuda.device(dev):
+        check(_lib.lib().uuo_nn_argmin_presorted(ptr(markers), ptr(vertices), ptr(ids), F, M, V, ptr(d), ptr(i), ptr(p),
+                                                 stream_ptr(dev)))
+    return (d, i, p) if want_pos else (d, i)
+
+
 def get_marker_mask(markers: torch.Tensor) -> torch.Tensor:
     """src/video_mocap/optimization.py:703-715 (float 0/1 instead of bool)."""
     markers = _req(markers, "markers")

@@ -181,6 +181,9 @@ class SMPL(torch.nn.Module):
         self.num_betas = num_betas
         self.batch_size = batch_size
         self.faces = np.asarray(faces)
+        self.extra_joint_ids = np.asarray(extra_joint_ids, dtype=np.int64)
+        self._twin = None
+        self.visit_ids = None          # set on a twin: int32 [V], original vertex id of every row of its output
         self.handle = ModelHandle(v_template, shapedirs, posedirs, J_regressor, weights, parents, extra_joint_ids, device)
         T = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt, device=device)
         self.register_buffer("faces_tensor", T(self.faces.astype(np.int64), torch.long))
@@ -194,6 +197,34 @@ class SMPL(torch.nn.Module):
     @property
     def device(self):
         return self.handle.device
+
+    def vertex_order(self) -> np.ndarray:
+        """The model's spatially coherent vertex permutation (uuo_model_vertex_order), as a host array."""
+        out = np.empty(self.handle.V, dtype=np.int32)
+        check(_lib.lib().uuo_model_vertex_order_host(self.handle.handle, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def visiting_twin(self) -> "SMPL":
+        """The same body with its vertices RENUMBERED in visiting order (row p of the twin's vertices is vertex
+        ``visit_ids[p]`` of this model).  The fitting loop runs the dense forward on the twin so that the
+        correspondence kernel streams tiles of 32 consecutive, spatially close vertices (uuo_nn_argmin_presorted);
+        joints and every per-frame quantity are unchanged.  Internal: never handed to the caller."""
+        if self._twin is None:
+            perm = self.vertex_order().astype(np.int64)
+            inv = np.empty_like(perm)
+            inv[perm] = np.arange(perm.shape[0])
+            V = perm.shape[0]
+            cpu = lambda t: t.detach().cpu().numpy()
+            pd = cpu(self.posedirs)                                                    # [P, 3V]
+            st = _Struct(v_template=cpu(self.v_template)[perm], shapedirs=cpu(self.shapedirs)[perm],
+                         posedirs=np.ascontiguousarray(pd.reshape(pd.shape[0], V, 3)[:, perm].reshape(pd.shape[0], 3 * V)),
+                         J_regressor=np.ascontiguousarray(cpu(self.J_regressor)[:, perm]),
+                         weights=cpu(self.lbs_weights)[perm], parents=cpu(self.parents), f=self.faces)
+            tw = SMPL(st, device=self.device, num_betas=self.num_betas, extra_joint_ids=inv[self.extra_joint_ids],
+                      batch_size=self.batch_size)
+            tw.visit_ids = torch.as_tensor(perm.astype(np.int32), device=self.device)
+            self._twin = tw
+        return self._twin
 
     def get_num_verts(self):
         return self.handle.V
