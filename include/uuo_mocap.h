@@ -91,6 +91,18 @@ int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int betas_rows
                           float* g_betas, float* g_global_orient, float* g_body_pose, float* g_yaw,
                           float* g_transl, void* stream);
 
+/* The same backward when the workspace already holds v_posed of these rows (R <= 64), which saves re-evaluating
+ * the 3R blend-shape dot products: either uuo_lbs_forward_rows ran on this workspace with the SAME rows, or
+ * uuo_lbs_cache_vposed_rows picked them out of the v_posed a dense uuo_lbs_forward left in the workspace
+ * (pos[F,R] = row of that forward's vertex array, e.g. the `pos` output of uuo_nn_argmin_presorted). */
+int uuo_lbs_backward_rows_cached(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                                 const float* body_pose, int pose_mode, const float* yaw, int F,
+                                 const int32_t* rows, int rows_shared, int R, const float* g_rows,
+                                 const float* g_joints, void* workspace,
+                                 float* g_betas, float* g_global_orient, float* g_body_pose, float* g_yaw,
+                                 float* g_transl, void* stream);
+int uuo_lbs_cache_vposed_rows(const uuo_model* m, int F, const int32_t* pos, int R, void* workspace, void* stream);
+
 /* Forward of R selected vertices only (marker stage, optimization.py:345-351 is a gather):
  * out_rows[F,R,3]; joints[F,J+NE,3] may be NULL. */
 int uuo_lbs_forward_rows(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,

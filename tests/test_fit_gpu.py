@@ -173,3 +173,74 @@ def test_stacked_hypotheses_equal_separate_fits(ctx):
         assert abs(s1[0] - scores[h]) <= 1e-4 * abs(s1[0])
         assert rel_err(fitted[h]["trans"].cpu().numpy(), f1[0]["trans"].cpu().numpy()) < 1e-4
     assert best == int(np.argmin(scores))
+
+
+@pytest.mark.parametrize("kind", ["top4", "dense"])
+@pytest.mark.parametrize("shared,R,F", [(True, 45, 130), (True, 7, 3), (False, 45, 70), (False, 64, 5), (True, 80, 9)])
+def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
+    """uuo_lbs_forward_rows == gather of the dense forward; uuo_lbs_backward_rows (re-evaluating v_posed) ==
+    uuo_lbs_backward_rows_cached (v_posed from the forward / from uuo_lbs_cache_vposed_rows) == the dense backward
+    fed a gradient that is non-zero on those rows only."""
+    from uuo_mocap_b200 import _lib, synthetic
+    from uuo_mocap_b200._lib import check, ptr, stream_ptr
+    from uuo_mocap_b200.smpl import SMPL, _as_struct, POSE_RAW6D
+    model = get_model(kind)
+    smpl = SMPL(_as_struct(model), device="cuda:0")
+    mh, dev, L = smpl.handle, torch.device("cuda:0"), _lib.lib()
+    V = mh.V
+    rng = np.random.default_rng(R * 100 + F)
+    mb = synthetic.make_lbs_microbench(F, seed=R)
+    rot = torch.from_numpy(mb["rot"] + 0.05 * rng.normal(size=mb["rot"].shape).astype(np.float32)).to(dev)
+    go, bp = rot[:, :1].contiguous(), rot[:, 1:].contiguous()
+    betas, transl = torch.from_numpy(mb["betas"][:1]).to(dev), torch.from_numpy(mb["transl"]).to(dev)
+    if shared:
+        rows = torch.from_numpy(rng.choice(V, size=R, replace=False).astype(np.int32)).to(dev)
+        rows_f = rows.long().unsqueeze(0).expand(F, R)
+    else:
+        rows = torch.from_numpy(rng.integers(0, V, size=(F, R)).astype(np.int32)).to(dev)
+        rows_f = rows.long()
+    g_rows = torch.from_numpy(rng.normal(size=(F, R, 3)).astype(np.float32)).to(dev)
+    g_rows[::2, ::5] = 0.0                                   # masked rows are skipped
+    ws, st = mh.workspace(F), stream_ptr(dev)
+    verts = torch.empty((F, V, 3), device=dev)
+    check(L.uuo_lbs_forward(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, ptr(transl), F, ptr(verts), None,
+                            ptr(ws), st))
+    # dense backward with the sparse gradient scattered (duplicates add up)
+    gv = torch.zeros((F, V, 3), device=dev)
+    gv.view(F * V, 3).index_add_(0, (rows_f + torch.arange(F, device=dev).unsqueeze(1) * V).reshape(-1), g_rows.view(-1, 3))
+    outs = {}
+
+    def grads():
+        return [torch.zeros_like(betas), torch.zeros_like(go), torch.zeros_like(bp), torch.zeros_like(transl)]
+    gd = grads()
+    check(L.uuo_lbs_backward(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(gv), None, ptr(ws),
+                             ptr(gd[0]), ptr(gd[1]), ptr(gd[2]), None, ptr(gd[3]), st))
+    outs["dense"] = gd
+    out_rows = torch.empty((F, R, 3), device=dev)
+    check(L.uuo_lbs_forward_rows(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, ptr(transl), F, ptr(rows),
+                                 1 if shared else 0, R, ptr(out_rows), None, ptr(ws), st))
+    ref_rows = torch.gather(verts, 1, rows_f.unsqueeze(-1).expand(F, R, 3))
+    assert rel_err(out_rows.cpu().numpy(), ref_rows.cpu().numpy()) < 1e-5
+    variants = [("recompute", L.uuo_lbs_backward_rows)]
+    if R <= 64:
+        variants.append(("cached", L.uuo_lbs_backward_rows_cached))
+    for name, fn in variants:
+        g = grads()
+        check(fn(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(rows), 1 if shared else 0, R,
+                 ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]), ptr(g[2]), None, ptr(g[3]), st))
+        outs[name] = g
+    if R <= 64:   # v_posed rows picked out of a dense forward's workspace by position (= vertex id on the model itself)
+        check(L.uuo_lbs_forward(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, ptr(transl), F, ptr(verts),
+                                None, ptr(ws), st))
+        pos = rows_f.to(torch.int32).contiguous()
+        check(L.uuo_lbs_cache_vposed_rows(mh.handle, F, ptr(pos), R, ptr(ws), st))
+        g = grads()
+        check(L.uuo_lbs_backward_rows_cached(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(rows),
+                                             1 if shared else 0, R, ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]),
+                                             ptr(g[2]), None, ptr(g[3]), st))
+        outs["cached_from_dense"] = g
+    for name, g in outs.items():
+        if name == "dense":
+            continue
+        for a, b, what in zip(g, outs["dense"], ("betas", "global_orient", "body_pose", "transl")):
+            assert rel_err(a.cpu().numpy(), b.cpu().numpy()) < 1e-4, (name, what)

@@ -27,6 +27,8 @@ SIGNATURES = {
     "uuo_lbs_forward": (_I, [_P, _P, _I, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P]),
     "uuo_lbs_backward": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "uuo_lbs_backward_rows": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "uuo_lbs_backward_rows_cached": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "uuo_lbs_cache_vposed_rows": (_I, [_P, _I, _P, _I, _P, _P]),
     "uuo_lbs_forward_rows": (_I, [_P, _P, _I, _P, _P, _I, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P]),
     "uuo_nn_argmin": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "uuo_nn_argmin_ordered": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),

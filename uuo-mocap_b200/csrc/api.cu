@@ -59,7 +59,7 @@ extern "C" int uuo_lbs_forward_rows(const uuo_model* m, const float* betas, int 
   return launch_rows_forward(m, transl, F, rows, rows_shared, R, out_rows, ws, st);
 }
 
-extern "C" int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int betas_rows,
+static int backward_rows_impl(int vposed_cached, const uuo_model* m, const float* betas, int betas_rows,
                                      const float* global_orient, const float* body_pose, int pose_mode,
                                      const float* yaw, int F, const int32_t* rows, int rows_shared, int R,
                                      const float* g_rows, const float* g_joints, void* workspace, float* g_betas,
@@ -71,7 +71,36 @@ extern "C" int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int
   UUO_CHECK_ARG(g_joints == nullptr || m->NE == 0, "g_joints on the rows path would touch the extra-joint vertices: pass NULL");
   cudaStream_t st = (cudaStream_t)stream;
   uuo_ws ws = carve_ws(m, F, workspace);
-  if ((rc = launch_rows_backward(m, F, rows, rows_shared, R, g_rows, ws, st))) return rc;
+  if ((rc = launch_rows_backward(m, F, rows, rows_shared, R, g_rows, vposed_cached, ws, st))) return rc;
   return launch_fk_backward(m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, F, g_joints, ws, 1, 1,
                             nullptr, g_betas, g_global_orient, g_body_pose, g_yaw, g_transl, st);
+}
+
+#define UUO_ROWS_ARGS m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, F, rows, rows_shared, R, g_rows, g_joints, \
+                      workspace, g_betas, g_global_orient, g_body_pose, g_yaw, g_transl, stream
+
+extern "C" int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int betas_rows,
+                                     const float* global_orient, const float* body_pose, int pose_mode,
+                                     const float* yaw, int F, const int32_t* rows, int rows_shared, int R,
+                                     const float* g_rows, const float* g_joints, void* workspace, float* g_betas,
+                                     float* g_global_orient, float* g_body_pose, float* g_yaw, float* g_transl,
+                                     void* stream) {
+  return backward_rows_impl(0, UUO_ROWS_ARGS);
+}
+
+extern "C" int uuo_lbs_backward_rows_cached(const uuo_model* m, const float* betas, int betas_rows,
+                                            const float* global_orient, const float* body_pose, int pose_mode,
+                                            const float* yaw, int F, const int32_t* rows, int rows_shared, int R,
+                                            const float* g_rows, const float* g_joints, void* workspace, float* g_betas,
+                                            float* g_global_orient, float* g_body_pose, float* g_yaw, float* g_transl,
+                                            void* stream) {
+  UUO_CHECK_ARG(R <= 64, "the cached v_posed rows hold at most 64 rows per frame");
+  return backward_rows_impl(1, UUO_ROWS_ARGS);
+}
+
+extern "C" int uuo_lbs_cache_vposed_rows(const uuo_model* m, int F, const int32_t* pos, int R, void* workspace,
+                                         void* stream) {
+  UUO_CHECK_ARG(m && pos && workspace && F > 0 && R > 0 && R <= 64, "bad arguments (R must be in [1,64])");
+  uuo_ws ws = carve_ws(m, F, workspace);
+  return launch_cache_vposed_rows(m, F, pos, R, ws, (cudaStream_t)stream);
 }

@@ -171,4 +171,5 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
 int launch_rows_forward(const uuo_model* m, const float* transl, int F, const int32_t* rows, int rows_shared,
                         int R, float* out_rows, const uuo_ws& ws, cudaStream_t st);
 int launch_rows_backward(const uuo_model* m, int F, const int32_t* rows, int rows_shared, int R,
-                         const float* g_rows, const uuo_ws& ws, cudaStream_t st);
+                         const float* g_rows, int vposed_cached, const uuo_ws& ws, cudaStream_t st);
+int launch_cache_vposed_rows(const uuo_model* m, int F, const int32_t* pos, int R, const uuo_ws& ws, cudaStream_t st);

@@ -2,163 +2,374 @@
 // only R vertex rows per frame.  This is what the fitting closures need:
 //   marker stage  : virtual markers = vertices[:, idx]   (optimization.py:345-351, a gather)
 //   chamfer stage : d loss / d vertices is non-zero only at the argmin rows (pytorch3d knn backward)
-// One warp per frame; lanes span the K = P + NB coefficients for the blend-shape dot products and the
-// 288 entries of dA for the skinning backward.  Frames are independent, rows are accumulated in order
-// (deterministic).  Nothing of size [F,V] is touched.
+// Nothing of size [F,V] is touched.  One warp per frame, frames independent, rows accumulated in order
+// (deterministic).  The per-row arithmetic (blend-shape dot products of length K = P + NB, the 24-joint
+// transform blend, the 3x4 apply) runs ONE ROW PER LANE -- no cross-lane reductions; the frame's coefficients
+// and transforms are staged in shared memory and read as broadcasts.  Only the two reductions OVER rows of the
+// backward (d coef, d A) run row by row with lanes across the coefficient / joint axis.
 #include "common.cuh"
 
 #define FULL 0xffffffffu
-#define ROWS_MAXK 8   // KP <= 256
+#define ROWS_WARPS 4
+#define ROWS_MAXKP 256      // KP <= 256
+#define ROWS_CHUNK 64       // rows staged per pass of the backward
 
-__device__ __forceinline__ float wsum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
-  return v;
+struct __align__(16) RowRec {
+  float vp[3];
+  int v;
+  float gvp[3];
+  float pad0;
+  float g[3];
+  float pad1;
+};
+
+// v_posed of row v for this lane: vt + coef . Bt[3v+c]   (lbs.py:226-233 for one vertex)
+__device__ __forceinline__ void lane_vposed(const float* __restrict__ vt, const float* __restrict__ Bt, int KP,
+                                            const float4* __restrict__ s_coef4, int v, float* vp) {
+  const float4* b0 = reinterpret_cast<const float4*>(Bt + (size_t)(3 * v) * KP);
+  const float4* b1 = b0 + (KP >> 2);
+  const float4* b2 = b1 + (KP >> 2);
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < (KP >> 2); ++k) {
+    const float4 c = s_coef4[k];
+    const float4 x = __ldg(b0 + k), y = __ldg(b1 + k), z = __ldg(b2 + k);
+    a0 = fmaf(c.x, x.x, a0); a0 = fmaf(c.y, x.y, a0); a0 = fmaf(c.z, x.z, a0); a0 = fmaf(c.w, x.w, a0);
+    a1 = fmaf(c.x, y.x, a1); a1 = fmaf(c.y, y.y, a1); a1 = fmaf(c.z, y.z, a1); a1 = fmaf(c.w, y.w, a1);
+    a2 = fmaf(c.x, z.x, a2); a2 = fmaf(c.y, z.y, a2); a2 = fmaf(c.z, z.z, a2); a2 = fmaf(c.w, z.w, a2);
+  }
+  vp[0] = a0 + vt[3 * v];
+  vp[1] = a1 + vt[3 * v + 1];
+  vp[2] = a2 + vt[3 * v + 2];
 }
 
-// v_posed of one vertex: vt + coef . Bt[3v+c]   (all lanes get the 3 results)
-__device__ __forceinline__ void row_vposed(const float* __restrict__ vt, const float* __restrict__ Bt, int KP,
-                                           const float* cf /*[ROWS_MAXK] per lane*/, int v, int lane, float* vp) {
+// blended transform of row v for this lane: T[ab] = sum_j W[v][j] A[j][ab]   (lbs.py:237-243), NAB = 12 or 9 (rotation only)
+template <bool WITH_T>
+__device__ __forceinline__ void lane_blend(const float* __restrict__ W, int J, const float4* __restrict__ s_A4, int v,
+                                           float* T /*[12]*/) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    const float* b = Bt + (size_t)(3 * v + c) * KP;
-    float a = 0.f;
+  for (int i = 0; i < 12; ++i) T[i] = 0.f;
+  const float4* w4 = reinterpret_cast<const float4*>(W + (size_t)v * J);   // J == 24: rows are 96 B, 16 B aligned
+  for (int j4 = 0; j4 < (J >> 2); ++j4) {
+    const float4 w = __ldg(w4 + j4);
+    const float ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-    for (int q = 0; q < ROWS_MAXK; ++q) {
-      int k = lane + 32 * q;
-      if (k < KP) a = fmaf(cf[q], b[k], a);
-    }
-    vp[c] = wsum(a) + vt[3 * v + c];
-  }
-}
-
-__global__ void __launch_bounds__(128) rows_forward_kernel(
-    const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
-    const float* __restrict__ coef, const float* __restrict__ A, const float* __restrict__ transl, int F,
-    const int32_t* __restrict__ rows, int rows_shared, int R, float* __restrict__ out_rows) {
-  const int lane = threadIdx.x & 31;
-  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (f >= F) return;
-  float cf[ROWS_MAXK];
-#pragma unroll
-  for (int q = 0; q < ROWS_MAXK; ++q) {
-    int k = lane + 32 * q;
-    cf[q] = (k < KP) ? coef[(size_t)f * KP + k] : 0.f;
-  }
-  const float* Af = A + (size_t)f * J * 12;
-  for (int r = 0; r < R; ++r) {
-    const int v = rows_shared ? rows[r] : rows[(size_t)f * R + r];
-    float vp[3];
-    row_vposed(vt, Bt, KP, cf, v, lane, vp);
-    // lane i < 12 owns T entry i
-    float t = 0.f;
-    if (lane < 12) {
-      for (int j = 0; j < J; ++j) t = fmaf(W[(size_t)v * J + j], Af[j * 12 + lane], t);
-    }
-    // out[a] = T[a][0..2].vp + T[a][3]
-    float contrib = 0.f;
-    if (lane < 12) {
-      int b = lane & 3;
-      contrib = (b < 3) ? t * vp[b] : t;
-    }
-    // sum the 4 lanes of each row a
-    contrib += __shfl_xor_sync(FULL, contrib, 1);
-    contrib += __shfl_xor_sync(FULL, contrib, 2);
-    if (lane < 12 && (lane & 3) == 0) {
-      int a = lane >> 2;
-      out_rows[((size_t)f * R + r) * 3 + a] = contrib + (transl ? transl[(size_t)f * 3 + a] : 0.f);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(128) rows_backward_kernel(
-    const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
-    const float* __restrict__ coef, const float* __restrict__ A, int F, const int32_t* __restrict__ rows,
-    int rows_shared, int R, const float* __restrict__ g_rows, float* __restrict__ gA_part,
-    float* __restrict__ gcoef_part) {
-  const int lane = threadIdx.x & 31;
-  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (f >= F) return;
-  float cf[ROWS_MAXK], gc[ROWS_MAXK];
-#pragma unroll
-  for (int q = 0; q < ROWS_MAXK; ++q) {
-    int k = lane + 32 * q;
-    cf[q] = (k < KP) ? coef[(size_t)f * KP + k] : 0.f;
-    gc[q] = 0.f;
-  }
-  float ga[9];   // dA entries e = lane + 32*q, e < 288
-#pragma unroll
-  for (int q = 0; q < 9; ++q) ga[q] = 0.f;
-  float gs = 0.f;  // lane a < 3: sum of g over rows
-  const float* Af = A + (size_t)f * J * 12;
-  for (int r = 0; r < R; ++r) {
-    const int v = rows_shared ? rows[r] : rows[(size_t)f * R + r];
-    const float* gp = g_rows + ((size_t)f * R + r) * 3;
-    const float g0 = gp[0], g1 = gp[1], g2 = gp[2];
-    if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;   // masked / dropped markers (warp-uniform)
-    float vp[3];
-    row_vposed(vt, Bt, KP, cf, v, lane, vp);
-    if (lane < 3) gs += (lane == 0 ? g0 : (lane == 1 ? g1 : g2));
-    // T[:3,:3] entries on lanes 0..8 (row a = lane/3, col b = lane%3)
-    float t = 0.f;
-    if (lane < 9) {
-      int a = lane / 3, b = lane % 3;
-      for (int j = 0; j < J; ++j) t = fmaf(W[(size_t)v * J + j], Af[j * 12 + a * 4 + b], t);
-    }
-    // g_vposed[c] = sum_a T[a][c] g[a]
-    float gvp[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      float t0 = __shfl_sync(FULL, t, c), t1 = __shfl_sync(FULL, t, 3 + c), t2 = __shfl_sync(FULL, t, 6 + c);
-      gvp[c] = t0 * g0 + t1 * g1 + t2 * g2;
-    }
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const float* b = Bt + (size_t)(3 * v + c) * KP;
-#pragma unroll
-      for (int q = 0; q < ROWS_MAXK; ++q) {
-        int k = lane + 32 * q;
-        if (k < KP) gc[q] = fmaf(gvp[c], b[k], gc[q]);
+    for (int i = 0; i < 4; ++i) {
+      const float4 r0 = s_A4[(j4 * 4 + i) * 3], r1 = s_A4[(j4 * 4 + i) * 3 + 1], r2 = s_A4[(j4 * 4 + i) * 3 + 2];
+      T[0] = fmaf(ws[i], r0.x, T[0]); T[1] = fmaf(ws[i], r0.y, T[1]); T[2] = fmaf(ws[i], r0.z, T[2]);
+      T[4] = fmaf(ws[i], r1.x, T[4]); T[5] = fmaf(ws[i], r1.y, T[5]); T[6] = fmaf(ws[i], r1.z, T[6]);
+      T[8] = fmaf(ws[i], r2.x, T[8]); T[9] = fmaf(ws[i], r2.y, T[9]); T[10] = fmaf(ws[i], r2.z, T[10]);
+      if (WITH_T) {
+        T[3] = fmaf(ws[i], r0.w, T[3]); T[7] = fmaf(ws[i], r1.w, T[7]); T[11] = fmaf(ws[i], r2.w, T[11]);
       }
     }
-    // dA[j][a][b] += W[v][j] g[a] vh[b]
+  }
+}
+
+// stage the frame's coefficients [KP] and relative transforms [J][12] into this warp's shared memory
+__device__ __forceinline__ void stage_frame(const float* __restrict__ coef, const float* __restrict__ A, int KP, int J,
+                                            int f, int lane, float* s_coef, float* s_A) {
+  const float4* c4 = reinterpret_cast<const float4*>(coef + (size_t)f * KP);
+  for (int i = lane; i < (KP >> 2); i += 32) reinterpret_cast<float4*>(s_coef)[i] = __ldg(c4 + i);
+  const float4* a4 = reinterpret_cast<const float4*>(A + (size_t)f * J * 12);
+  for (int i = lane; i < J * 3; i += 32) reinterpret_cast<float4*>(s_A)[i] = __ldg(a4 + i);
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(ROWS_WARPS * 32) rows_forward_kernel(
+    const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
+    const float* __restrict__ coef, const float* __restrict__ A, const float* __restrict__ transl, int F,
+    const int32_t* __restrict__ rows, int rows_shared, int R, float* __restrict__ out_rows,
+    float* __restrict__ rowbuf /* [F][ROWS_CHUNK][4] v_posed of the rows, or NULL */) {
+  __shared__ __align__(16) float s_coef_all[ROWS_WARPS][ROWS_MAXKP];
+  __shared__ __align__(16) float s_A_all[ROWS_WARPS][UUO_SKIN_J * 12];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int f = blockIdx.x * ROWS_WARPS + w;
+  if (f >= F) return;
+  stage_frame(coef, A, KP, J, f, lane, s_coef_all[w], s_A_all[w]);
+  const float4* s_coef4 = reinterpret_cast<const float4*>(s_coef_all[w]);
+  const float4* s_A4 = reinterpret_cast<const float4*>(s_A_all[w]);
+  float tr[3] = {0.f, 0.f, 0.f};
+  if (transl) { tr[0] = transl[(size_t)f * 3]; tr[1] = transl[(size_t)f * 3 + 1]; tr[2] = transl[(size_t)f * 3 + 2]; }
+  for (int r0 = 0; r0 < R; r0 += 32) {
+    const int r = r0 + lane;
+    if (r >= R) break;
+    const int v = rows_shared ? rows[r] : rows[(size_t)f * R + r];
+    float vp[3], T[12];
+    lane_vposed(vt, Bt, KP, s_coef4, v, vp);
+    if (rowbuf) reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(vp[0], vp[1], vp[2], 0.f);
+    lane_blend<true>(W, J, s_A4, v, T);
+    float* o = out_rows + ((size_t)f * R + r) * 3;
 #pragma unroll
-    for (int q = 0; q < 9; ++q) {
-      int e = lane + 32 * q;
-      int j = e / 12, ab = e % 12, a = ab >> 2, b = ab & 3;
-      float ga_ = (a == 0 ? g0 : (a == 1 ? g1 : g2));
-      float vh = (b == 0 ? vp[0] : (b == 1 ? vp[1] : (b == 2 ? vp[2] : 1.f)));
-      ga[q] = fmaf(W[(size_t)v * J + j] * ga_, vh, ga[q]);
+    for (int a = 0; a < 3; ++a)
+      o[a] = fmaf(T[a * 4], vp[0], fmaf(T[a * 4 + 1], vp[1], fmaf(T[a * 4 + 2], vp[2], T[a * 4 + 3]))) + tr[a];
+  }
+}
+
+// ---- forward for rows SHARED by all frames (marker stage: the same M vertices in every frame) ----
+// Persistent CTAs keep the 3R selected rows of Bt in shared memory (pitch KP+1: conflict-free when lanes
+// walk different rows at the same k), so the blend-shape part is a small GEMM out of shared memory:
+// lanes across the 3R outputs, the frame's coefficients broadcast.  Then one row per lane for the blend.
+#define ROWSS_WARPS 8
+#define ROWSS_NI 6            // 3R <= 192
+
+struct rowss_layout {
+  int pitch, n3;
+  size_t off_vt, off_w, off_coef, off_A, off_vp, total;
+};
+__host__ __device__ inline rowss_layout rowss_make_layout(int KP, int R, int J) {
+  rowss_layout L;
+  L.pitch = KP + 1;
+  L.n3 = 3 * R;
+  L.off_vt = (size_t)L.n3 * L.pitch * 4;
+  L.off_w = L.off_vt + (size_t)((L.n3 + 3) & ~3) * 4;
+  L.off_coef = (L.off_w + (size_t)R * J * 4 + 15) & ~(size_t)15;
+  L.off_A = L.off_coef + (size_t)ROWSS_WARPS * ROWS_MAXKP * 4;
+  L.off_vp = L.off_A + (size_t)ROWSS_WARPS * UUO_SKIN_J * 12 * 4;
+  L.total = L.off_vp + (size_t)ROWSS_WARPS * 32 * ROWSS_NI * 4;
+  return L;
+}
+
+__global__ void __launch_bounds__(ROWSS_WARPS * 32, 1) rows_forward_shared_kernel(
+    const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
+    const float* __restrict__ coef, const float* __restrict__ A, const float* __restrict__ transl, int F,
+    const int32_t* __restrict__ rows, int R, float* __restrict__ out_rows, float* __restrict__ rowbuf) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const rowss_layout L = rowss_make_layout(KP, R, J);
+  float* s_B = reinterpret_cast<float*>(smem_raw);                     // [3R][KP+1]
+  float* s_vt = reinterpret_cast<float*>(smem_raw + L.off_vt);         // [3R]
+  float* s_W = reinterpret_cast<float*>(smem_raw + L.off_w);           // [R][J]
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  float* s_coef = reinterpret_cast<float*>(smem_raw + L.off_coef) + w * ROWS_MAXKP;
+  float* s_A = reinterpret_cast<float*>(smem_raw + L.off_A) + w * UUO_SKIN_J * 12;
+  float* s_vp = reinterpret_cast<float*>(smem_raw + L.off_vp) + w * 32 * ROWSS_NI;
+  const int n3 = L.n3, pitch = L.pitch;
+  for (int i = tid; i < n3 * KP; i += ROWSS_WARPS * 32) {
+    const int n = i / KP, k = i - n * KP;
+    s_B[n * pitch + k] = __ldg(Bt + (size_t)(3 * rows[n / 3] + n % 3) * KP + k);
+  }
+  for (int i = tid; i < n3; i += ROWSS_WARPS * 32) s_vt[i] = vt[3 * rows[i / 3] + i % 3];
+  for (int i = tid; i < R * J; i += ROWSS_WARPS * 32) s_W[i] = W[(size_t)rows[i / J] * J + i % J];
+  __syncthreads();
+  const float4* s_coef4 = reinterpret_cast<const float4*>(s_coef);
+  const float4* s_A4 = reinterpret_cast<const float4*>(s_A);
+  for (int f = blockIdx.x * ROWSS_WARPS + w; f < F; f += gridDim.x * ROWSS_WARPS) {
+    stage_frame(coef, A, KP, J, f, lane, s_coef, s_A);
+    // v_posed of the 3R outputs: lane owns n = lane + 32 i
+    float acc[ROWSS_NI];
+    const float* bp[ROWSS_NI];
+#pragma unroll
+    for (int i = 0; i < ROWSS_NI; ++i) {
+      acc[i] = 0.f;
+      bp[i] = s_B + min(lane + 32 * i, n3 - 1) * pitch;
     }
+    for (int k4 = 0; k4 < (KP >> 2); ++k4) {
+      const float4 c = s_coef4[k4];
+#pragma unroll
+      for (int i = 0; i < ROWSS_NI; ++i) {
+        if (32 * i < n3) {
+          const float* b = bp[i] + 4 * k4;
+          acc[i] = fmaf(c.x, b[0], acc[i]);
+          acc[i] = fmaf(c.y, b[1], acc[i]);
+          acc[i] = fmaf(c.z, b[2], acc[i]);
+          acc[i] = fmaf(c.w, b[3], acc[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < ROWSS_NI; ++i) {
+      const int n = lane + 32 * i;
+      if (n < n3) s_vp[n] = acc[i] + s_vt[n];
+    }
+    __syncwarp();
+    float tr[3] = {0.f, 0.f, 0.f};
+    if (transl) { tr[0] = transl[(size_t)f * 3]; tr[1] = transl[(size_t)f * 3 + 1]; tr[2] = transl[(size_t)f * 3 + 2]; }
+    for (int r = lane; r < R; r += 32) {
+      const float vp0 = s_vp[3 * r], vp1 = s_vp[3 * r + 1], vp2 = s_vp[3 * r + 2];
+      if (rowbuf) reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(vp0, vp1, vp2, 0.f);
+      float T[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) T[i] = 0.f;
+      for (int j = 0; j < J; ++j) {
+        const float wj = s_W[r * J + j];
+        const float4 r0 = s_A4[j * 3], r1 = s_A4[j * 3 + 1], r2 = s_A4[j * 3 + 2];
+        T[0] = fmaf(wj, r0.x, T[0]); T[1] = fmaf(wj, r0.y, T[1]); T[2] = fmaf(wj, r0.z, T[2]); T[3] = fmaf(wj, r0.w, T[3]);
+        T[4] = fmaf(wj, r1.x, T[4]); T[5] = fmaf(wj, r1.y, T[5]); T[6] = fmaf(wj, r1.z, T[6]); T[7] = fmaf(wj, r1.w, T[7]);
+        T[8] = fmaf(wj, r2.x, T[8]); T[9] = fmaf(wj, r2.y, T[9]); T[10] = fmaf(wj, r2.z, T[10]); T[11] = fmaf(wj, r2.w, T[11]);
+      }
+      float* o = out_rows + ((size_t)f * R + r) * 3;
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+        o[a] = fmaf(T[a * 4], vp0, fmaf(T[a * 4 + 1], vp1, fmaf(T[a * 4 + 2], vp2, T[a * 4 + 3]))) + tr[a];
+    }
+    __syncwarp();
+  }
+}
+
+// rowbuf[f][r] = v_posed rows of a dense forward (ws.vposed), picked by position
+__global__ void cache_vposed_rows_kernel(const float* __restrict__ vposed, int NP, int F, const int32_t* __restrict__ pos,
+                                         int R, float* __restrict__ rowbuf) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F * R) return;
+  const int f = i / R, r = i - f * R;
+  const float* p = vposed + (size_t)f * NP + 3 * pos[i];
+  reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(p[0], p[1], p[2], 0.f);
+}
+
+template <bool CACHED>
+__global__ void __launch_bounds__(ROWS_WARPS * 32) rows_backward_kernel(
+    const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
+    const float* __restrict__ coef, const float* __restrict__ A, int F, const int32_t* __restrict__ rows,
+    int rows_shared, int R, const float* __restrict__ g_rows, const float* __restrict__ rowbuf,
+    float* __restrict__ gA_part, float* __restrict__ gcoef_part) {
+  __shared__ __align__(16) float s_coef_all[ROWS_WARPS][ROWS_MAXKP];
+  __shared__ __align__(16) float s_A_all[ROWS_WARPS][UUO_SKIN_J * 12];
+  __shared__ RowRec s_rec_all[ROWS_WARPS][ROWS_CHUNK];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int f = blockIdx.x * ROWS_WARPS + w;
+  if (f >= F) return;
+  stage_frame(coef, A, KP, J, f, lane, s_coef_all[w], s_A_all[w]);
+  const float4* s_coef4 = reinterpret_cast<const float4*>(s_coef_all[w]);
+  const float4* s_A4 = reinterpret_cast<const float4*>(s_A_all[w]);
+  RowRec* rec = s_rec_all[w];
+  float gc[ROWS_MAXKP / 32];   // d coef, k = lane + 32 q
+#pragma unroll
+  for (int q = 0; q < ROWS_MAXKP / 32; ++q) gc[q] = 0.f;
+  float ga[12];                // d A[j = lane][ab]
+#pragma unroll
+  for (int i = 0; i < 12; ++i) ga[i] = 0.f;
+  float gs = 0.f;              // lane a < 3: sum of g over rows (d transl)
+  const int nq = KP >> 5;
+
+  for (int c0 = 0; c0 < R; c0 += ROWS_CHUNK) {
+    const int nc = min(ROWS_CHUNK, R - c0);
+    // ---- A. one row per lane: v_posed, rotation part of the blended transform, d v_posed = T^T g
+    for (int r0 = 0; r0 < nc; r0 += 32) {
+      const int r = r0 + lane;
+      if (r < nc) {
+        const int v = rows_shared ? rows[c0 + r] : rows[(size_t)f * R + c0 + r];
+        const float* gp = g_rows + ((size_t)f * R + c0 + r) * 3;
+        const float g0 = gp[0], g1 = gp[1], g2 = gp[2];
+        RowRec o;
+        o.v = v; o.g[0] = g0; o.g[1] = g1; o.g[2] = g2; o.pad0 = 0.f; o.pad1 = 0.f;
+        if (g0 == 0.f && g1 == 0.f && g2 == 0.f) {        // masked / dropped markers contribute nothing
+          o.v = -1;
+          o.vp[0] = o.vp[1] = o.vp[2] = o.gvp[0] = o.gvp[1] = o.gvp[2] = 0.f;
+        } else {
+          float T[12];
+          if (CACHED) {        // R <= ROWS_CHUNK: written by the forward of these very rows
+            const float4 c = reinterpret_cast<const float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r];
+            o.vp[0] = c.x; o.vp[1] = c.y; o.vp[2] = c.z;
+          } else {
+            lane_vposed(vt, Bt, KP, s_coef4, v, o.vp);
+          }
+          lane_blend<false>(W, J, s_A4, v, T);
+#pragma unroll
+          for (int c = 0; c < 3; ++c) o.gvp[c] = T[c] * g0 + T[4 + c] * g1 + T[8 + c] * g2;
+        }
+        rec[r] = o;
+      }
+    }
+    __syncwarp();
+    // ---- B. reductions over rows: lanes across coefficients (d coef) and joints (d A)
+    for (int r = 0; r < nc; ++r) {
+      const float4 q0 = reinterpret_cast<const float4*>(rec + r)[0];   // vp, v
+      const int v = __float_as_int(q0.w);
+      if (v < 0) continue;                                              // warp-uniform
+      const float4 q1 = reinterpret_cast<const float4*>(rec + r)[1];   // gvp
+      const float4 q2 = reinterpret_cast<const float4*>(rec + r)[2];   // g
+      const float* b = Bt + (size_t)(3 * v) * KP + lane;
+#pragma unroll
+      for (int q = 0; q < ROWS_MAXKP / 32; ++q)
+        if (q < nq) {
+          gc[q] = fmaf(q1.x, __ldg(b + 32 * q), gc[q]);
+          gc[q] = fmaf(q1.y, __ldg(b + KP + 32 * q), gc[q]);
+          gc[q] = fmaf(q1.z, __ldg(b + 2 * KP + 32 * q), gc[q]);
+        }
+      if (lane < 3) gs += lane == 0 ? q2.x : (lane == 1 ? q2.y : q2.z);
+      // dA[j][a][b] += W[v][j] g[a] vh[b],  vh = (v_posed, 1)
+      const float wj = lane < J ? __ldg(W + (size_t)v * J + lane) : 0.f;
+      const float gg[3] = {q2.x, q2.y, q2.z};
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const float wg = wj * gg[a];
+        ga[a * 4] = fmaf(wg, q0.x, ga[a * 4]);
+        ga[a * 4 + 1] = fmaf(wg, q0.y, ga[a * 4 + 1]);
+        ga[a * 4 + 2] = fmaf(wg, q0.z, ga[a * 4 + 2]);
+        ga[a * 4 + 3] += wg;
+      }
+    }
+    __syncwarp();
   }
   float* dstA = gA_part + (size_t)f * UUO_GA_STRIDE;
-#pragma unroll
-  for (int q = 0; q < 9; ++q) dstA[lane + 32 * q] = ga[q];
-  if (lane < 4) dstA[288 + lane] = (lane < 3) ? gs : 0.f;
+  if (lane < J) {
+    float4* d4 = reinterpret_cast<float4*>(dstA + lane * 12);
+    d4[0] = make_float4(ga[0], ga[1], ga[2], ga[3]);
+    d4[1] = make_float4(ga[4], ga[5], ga[6], ga[7]);
+    d4[2] = make_float4(ga[8], ga[9], ga[10], ga[11]);
+  }
+  if (lane < 4) dstA[J * 12 + lane] = (lane < 3) ? gs : 0.f;
   float* dstC = gcoef_part + (size_t)f * KP;
 #pragma unroll
-  for (int q = 0; q < ROWS_MAXK; ++q) {
-    int k = lane + 32 * q;
-    if (k < KP) dstC[k] = gc[q];
-  }
+  for (int q = 0; q < ROWS_MAXKP / 32; ++q)
+    if (q < nq) dstC[lane + 32 * q] = gc[q];
+}
+
+static int rows_check(const uuo_model* m) {
+  if (m->KP > ROWS_MAXKP || (m->KP & 31)) { uuo_set_error("rows path: KP must be a multiple of 32, <= 256"); return UUO_ERR_ARG; }
+  if (m->J != UUO_SKIN_J) { uuo_set_error("rows path: J must be 24"); return UUO_ERR_ARG; }
+  return UUO_OK;
 }
 
 int launch_rows_forward(const uuo_model* m, const float* transl, int F, const int32_t* rows, int rows_shared,
                         int R, float* out_rows, const uuo_ws& ws, cudaStream_t st) {
-  if (m->KP > 32 * ROWS_MAXK) { uuo_set_error("rows path: KP too large"); return UUO_ERR_ARG; }
-  { ProfScope ps_("rows_forward", st);
-  rows_forward_kernel<<<(F + 3) / 4, 128, 0, st>>>(m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows,
-                                                   rows_shared, R, out_rows);
-  } UUO_LAUNCH_CHECK();
+  int rc = rows_check(m);
+  if (rc) return rc;
+  float* rowbuf = R <= ROWS_CHUNK ? ws.rowbuf : nullptr;
+  const rowss_layout L = rowss_make_layout(m->KP, R, m->J);
+  ProfScope ps_("rows_forward", st);
+  if (rows_shared && 3 * R <= 32 * ROWSS_NI && L.total <= 227 * 1024 && F >= 64) {
+    static thread_local size_t configured = 0;
+    static thread_local int n_sm = 0;
+    if (L.total > configured) {
+      UUO_CUDA(cudaFuncSetAttribute(rows_forward_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+      configured = L.total;
+    }
+    if (!n_sm) {
+      int dev = 0;
+      UUO_CUDA(cudaGetDevice(&dev));
+      UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int need = (F + ROWSS_WARPS - 1) / ROWSS_WARPS;
+    rows_forward_shared_kernel<<<need < n_sm ? need : n_sm, ROWSS_WARPS * 32, L.total, st>>>(
+        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows, R, out_rows, rowbuf);
+  } else {
+    rows_forward_kernel<<<(F + ROWS_WARPS - 1) / ROWS_WARPS, ROWS_WARPS * 32, 0, st>>>(
+        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows, rows_shared, R, out_rows, rowbuf);
+  }
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+int launch_cache_vposed_rows(const uuo_model* m, int F, const int32_t* pos, int R, const uuo_ws& ws, cudaStream_t st) {
+  if (R > ROWS_CHUNK) { uuo_set_error("cache_vposed_rows: R must be <= 64"); return UUO_ERR_ARG; }
+  cache_vposed_rows_kernel<<<(F * R + 255) / 256, 256, 0, st>>>(ws.vposed, m->NP, F, pos, R, ws.rowbuf);
+  UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
 
 int launch_rows_backward(const uuo_model* m, int F, const int32_t* rows, int rows_shared, int R,
-                         const float* g_rows, const uuo_ws& ws, cudaStream_t st) {
-  if (m->KP > 32 * ROWS_MAXK) { uuo_set_error("rows path: KP too large"); return UUO_ERR_ARG; }
+                         const float* g_rows, int vposed_cached, const uuo_ws& ws, cudaStream_t st) {
+  int rc = rows_check(m);
+  if (rc) return rc;
+  if (vposed_cached && R > ROWS_CHUNK) { uuo_set_error("rows backward: cached v_posed needs R <= 64"); return UUO_ERR_ARG; }
   { ProfScope ps_("rows_backward", st);
-  rows_backward_kernel<<<(F + 3) / 4, 128, 0, st>>>(m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, F, rows,
-                                                    rows_shared, R, g_rows, ws.gA, ws.gcoef);
+  if (vposed_cached)
+    rows_backward_kernel<true><<<(F + ROWS_WARPS - 1) / ROWS_WARPS, ROWS_WARPS * 32, 0, st>>>(
+        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, F, rows, rows_shared, R, g_rows, ws.rowbuf, ws.gA, ws.gcoef);
+  else
+    rows_backward_kernel<false><<<(F + ROWS_WARPS - 1) / ROWS_WARPS, ROWS_WARPS * 32, 0, st>>>(
+        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, F, rows, rows_shared, R, g_rows, ws.rowbuf, ws.gA, ws.gcoef);
   } UUO_LAUNCH_CHECK();
   return UUO_OK;
 }

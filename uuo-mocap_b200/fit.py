@@ -92,9 +92,18 @@ class FitProblem:
                                               ptr(self.virt), None, ptr(self.ws), self._st()))
         return self.virt
 
-    def lbs_backward_rows(self, betas_rows, root, pose, yaw, rows, shared, g_rows, g_betas, g_root, g_pose, g_yaw, g_trans):
+    def lbs_backward_rows(self, betas_rows, root, pose, yaw, rows, shared, g_rows, g_betas, g_root, g_pose, g_yaw, g_trans,
+                          cached_pos=None, cached=False):
+        """``cached``: the workspace holds v_posed of these rows (uuo_lbs_forward_rows just ran with them);
+        ``cached_pos`` [F,R]: pick them out of the dense forward's v_posed first (chamfer stage)."""
         R = rows.shape[-1]
-        check(_lib.lib().uuo_lbs_backward_rows(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
+        fn = _lib.lib().uuo_lbs_backward_rows
+        if R <= 64 and (cached or cached_pos is not None):
+            if cached_pos is not None:
+                check(_lib.lib().uuo_lbs_cache_vposed_rows(self.twin.handle.handle, self.F, ptr(cached_pos), R, ptr(self.ws),
+                                                           self._st()))
+            fn = _lib.lib().uuo_lbs_backward_rows_cached
+        check(fn(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
                                                POSE_RAW6D, ptr(yaw), self.F, ptr(rows), 1 if shared else 0, R,
                                                ptr(g_rows), None, ptr(self.ws), ptr(g_betas), ptr(g_root), ptr(g_pose),
                                                ptr(g_yaw), ptr(g_trans), self._st()))
@@ -172,7 +181,7 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
             prob.idx.zero_()
             prob.pos.zero_()
         prob.lbs_backward_rows(brows, root_orient, v["pose_body"], v["z_angle"], prob.idx, False, prob.g_rows,
-                               prob.gbetas_target(), None, g["pose_body"], g["z_angle"], g["trans"])
+                               prob.gbetas_target(), None, g["pose_body"], g["z_angle"], g["trans"], cached_pos=prob.pos)
         if "reg_pose_body" in losses:                                                   # :243-245
             prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
                         g["pose_body"])
@@ -213,7 +222,7 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
         else:
             prob.g_rows.zero_()
         prob.lbs_backward_rows(brows, v["root_orient"], v["pose_body"], None, vertex_idx, True, prob.g_rows,
-                               prob.gbetas_target(), g["root_orient"], g["pose_body"], None, g["trans"])
+                               prob.gbetas_target(), g["root_orient"], g["pose_body"], None, g["trans"], cached=True)
         if "reg_pose_body" in losses:                                                   # :363-365
             prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
                         g["pose_body"])
