@@ -1,0 +1,40 @@
+"""Per-phase cycle breakdown of the presorted correspondence kernel (CTA 0).  Needs a library built with
+    UUO_EXTRA_NVCC_FLAGS=-DNP_TIMING python -m uuo_mocap_b200.build --force
+then: python tools/nn_phases.py [frames]"""
+import ctypes as C
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+import uuo_mocap_b200  # noqa: F401
+from uuo_mocap_b200 import _lib, ops, synthetic
+from uuo_mocap_b200.smpl import SMPL, _as_struct
+
+F = int(sys.argv[1]) if len(sys.argv) > 1 else 5000
+model = synthetic.make_model("top4")
+smpl = SMPL(_as_struct(model), device="cuda:0")
+twin = smpl.visiting_twin()
+cap = synthetic.make_capture(model, F, num_markers=41, seed=3, n_ghost=4, dropout_p=0.05, noise_std=0.002)
+rot = torch.from_numpy(synthetic.axis_angle_to_matrix_np(cap.gt_pose_aa.astype(np.float64)).astype(np.float32)).cuda()
+out = twin(betas=torch.from_numpy(cap.gt_betas).cuda(), body_pose=rot[:, 1:], global_orient=rot[:, :1],
+           transl=torch.from_numpy(cap.gt_trans).cuda(), pose2rot=False)
+v = out.vertices.detach().contiguous()
+mk = torch.from_numpy(cap.markers).cuda()
+L = C.CDLL(_lib.LIB_PATH)
+for _ in range(3):
+    ops.nn_argmin_presorted(mk, v, twin.visit_ids)
+torch.cuda.synchronize()
+L.uuo_debug_nn_phases(None, 1)
+ops.nn_argmin_presorted(mk, v, twin.visit_ids)
+torch.cuda.synchronize()
+buf = (C.c_ulonglong * 8)()
+L.uuo_debug_nn_phases(buf, 0)
+n = max(1, buf[7])
+names = ["wait frame", "tile boxes", "round boxes + markers", "3a bound + pairs", "3b drain pairs", "3c results"]
+tot = sum(buf[i] for i in range(6))
+for i, nm in enumerate(names):
+    print("%-24s %8.0f cycles/frame  %5.1f %%" % (nm, buf[i] / n, 100.0 * buf[i] / tot))
+print("frames on CTA 0: %d, cycles/frame %.0f, pairs/frame %.1f" % (n, tot / n, buf[6] / n))

@@ -273,10 +273,31 @@ extern "C" int uuo_nn_argmin_ordered(const float* markers, const float* vertices
 //   - 3a: one warp per marker finds the closest round, the closest tile in it, evaluates that tile (an
 //     exact distance that bounds everything else) and appends every other (marker, tile) pair whose box
 //     bound does not exceed it to a work list in shared memory;
-//   - 3b: all warps drain the list, one pair per warp at a time (balanced however hard a marker is), merging
+//   - 3b: all warps drain the list, one lane per half pair (16 vertices walked serially with a rotated start, so the
+//     stride-3 reads of 32 different tiles never collide on a bank), balanced however hard a marker is, merging
 //     with atomicMin on a packed 64-bit key  distance bits | original id | position  -- the lexicographic
 //     minimum the reference's first-minimum scan returns.
 // =====================================================================================================
+// per-phase cycle counters of CTA 0 (tools/nn_phases.py): compile with -DNP_TIMING
+#ifdef NP_TIMING
+__device__ unsigned long long np_phase_cycles[8];
+#define NP_TICK(i)                                                     \
+  do {                                                                 \
+    if (blockIdx.x == 0 && threadIdx.x == 0) {                         \
+      const long long now_ = clock64();                                \
+      np_phase_cycles[i] += (unsigned long long)(now_ - tick_);        \
+      tick_ = now_;                                                    \
+    }                                                                  \
+  } while (0)
+extern "C" int uuo_debug_nn_phases(unsigned long long* out, int reset) {
+  if (out) cudaMemcpyFromSymbol(out, np_phase_cycles, sizeof(np_phase_cycles));
+  if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(np_phase_cycles, z, sizeof(z)); }
+  return 0;
+}
+#else
+#define NP_TICK(i) do { } while (0)
+#endif
+
 #define NP_THREADS 1024
 #define NP_MAXM 256          // markers per pass over a frame
 #define NP_LIST 4096         // (marker, tile) pairs; overflow is evaluated inline by the producing warp
@@ -384,6 +405,9 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   if ((int)blockIdx.x < F) issue_load(blockIdx.x, 0);
 
   int buf = 0;
+#ifdef NP_TIMING
+  long long tick_ = clock64();
+#endif
   for (int f = blockIdx.x; f < F; f += gridDim.x, buf ^= 1) {
     // the other buffer was last read during the previous frame, which ended with a barrier
     if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
@@ -391,20 +415,34 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     else if (f + (int)gridDim.x < F && !hull_ok(f + gridDim.x)) asm volatile("cp.async.wait_group 1;" ::: "memory");
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    NP_TICK(0);   // wait for the frame
     const float* raw = stage0 + (size_t)buf * L.stage_floats +
                        (int)((reinterpret_cast<uintptr_t>(vertices + (size_t)f * nflt) & 15) >> 2);
-    // ---- 2. tile boxes: one warp per tile, stride-3 reads (conflict-free)
-    for (int t = warp; t < ntp; t += nwarp) {
-      const float* p = raw + 3 * min(t * 32 + lane, V - 1);     // the tail repeats the last vertex
-      const float x = p[0], y = p[1], z = p[2];
-      const float lx = redux_min_f32(x), ly = redux_min_f32(y), lz = redux_min_f32(z);
-      const float hx = redux_max_f32(x), hy = redux_max_f32(y), hz = redux_max_f32(z);
-      if (lane == 0) {
+    // ---- 2. tile boxes: one lane per HALF tile (16 vertices walked serially), 16 tiles per warp.  Lane l starts its
+    // walk at vertex (l & 15): at every step the 16 lanes of a half read 16 different residues of 3j mod 32 and the
+    // other half sits 48 words = 16 banks further, so the stride-96-word tiles never collide on a bank.
+    for (int tb = warp * 16; tb < ntp; tb += nwarp * 16) {
+      const int t = tb + (lane & 15), rot = lane & 15;
+      const int p0 = t * 32 + (lane >> 4) * 16;
+      float lx = INF, ly = INF, lz = INF, hx = -INF, hy = -INF, hz = -INF;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float* p = raw + 3 * min(p0 + ((i + rot) & 15), V - 1);     // the tail repeats the last vertex
+        const float x = p[0], y = p[1], z = p[2];
+        lx = fminf(lx, x); hx = fmaxf(hx, x);
+        ly = fminf(ly, y); hy = fmaxf(hy, y);
+        lz = fminf(lz, z); hz = fmaxf(hz, z);
+      }
+      lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, 16)); hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, 16));
+      ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, 16)); hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, 16));
+      lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, 16)); hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, 16));
+      if (lane < 16) {
         box[t] = lx; box[ntp + t] = ly; box[2 * ntp + t] = lz;
         box[3 * ntp + t] = hx; box[4 * ntp + t] = hy; box[5 * ntp + t] = hz;
       }
     }
     __syncthreads();
+    NP_TICK(1);   // tile boxes
     for (int r = warp; r < nr; r += nwarp) {
       const int t = r * 32 + lane;
       const float lx = redux_min_f32(box[t]), ly = redux_min_f32(box[ntp + t]), lz = redux_min_f32(box[2 * ntp + t]);
@@ -420,6 +458,7 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
       for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
       if (tid == 0) list_count = 0;
       __syncthreads();                                   // round boxes, markers, counter
+      NP_TICK(2);
       // ---- 3a. bound + candidate pairs, one warp per marker
       for (int m = warp; m < mc; m += nwarp) {
         const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
@@ -460,14 +499,40 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
         }
       }
       __syncthreads();
-      // ---- 3b. drain the pair list, one pair per warp at a time
+      NP_TICK(3);   // 3a
+      // ---- 3b. drain the pair list: one lane per HALF pair (16 vertices walked serially, rotated start as in step 2:
+      // no bank conflicts whatever the tiles are), 16 pairs per warp; the lane-local lexicographic minimum of
+      // (distance, original id) is merged with one atomicMin
       const int np = (int)min(list_count, (unsigned)NP_LIST);
-      for (int q = warp; q < np; q += nwarp) {
-        const unsigned e = list[q];
-        const int m = (int)(e >> 16), t = (int)(e & 0xffffu);
-        np_eval_merge(raw, ids, V, t, lane, mk[3 * m], mk[3 * m + 1], mk[3 * m + 2], key + m);
+      for (int qb = warp * 16; qb < np; qb += nwarp * 16) {
+        const int q = qb + (lane & 15), rot = lane & 15;
+        if (q < np) {
+          const unsigned e = list[q];
+          const int m = (int)(e >> 16), t = (int)(e & 0xffffu);
+          const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
+          const int p0 = t * 32 + (lane >> 4) * 16;
+          float dbest = INF;
+          int pbest = -1;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int pos = min(p0 + ((i + rot) & 15), V - 1);
+            const float* p = raw + 3 * pos;
+            const float d = nt_sqdist(mx, my, mz, p[0], p[1], p[2]);
+            if (d < dbest) { dbest = d; pbest = pos; }
+            else if (d == dbest && pbest >= 0 && pos != pbest) {          // exact tie inside the half tile: original ids decide
+              const int ia = ids ? __ldg(ids + pos) : pos, ib = ids ? __ldg(ids + pbest) : pbest;
+              if (ia < ib) pbest = pos;
+            }
+          }
+          if (pbest >= 0 && __float_as_uint(dbest) < 0x7f800000u) {        // inf / NaN never win
+            const int id = ids ? __ldg(ids + pbest) : pbest;
+            const unsigned long long k = np_pack(dbest, id, pbest);
+            if (k < *reinterpret_cast<volatile unsigned long long*>(key + m)) atomicMin(key + m, k);
+          }
+        }
       }
       __syncthreads();
+      NP_TICK(4);   // 3b
       // ---- 3c. results
       for (int m = tid; m < mc; m += nthr) {
         const unsigned long long k = key[m];
@@ -480,6 +545,10 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
       if (m0 + NP_MAXM < M) __syncthreads();
     }
     __syncthreads();                                     // every warp is done with this frame's buffer
+    NP_TICK(5);   // 3c
+#ifdef NP_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0) { np_phase_cycles[6] += list_count; np_phase_cycles[7] += 1; }
+#endif
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
