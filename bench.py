@@ -30,6 +30,17 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
+# Libraries (NCCL's version banner, torch warnings) may write to fd 1; the contract is ONE JSON line on stdout.
+# Keep the real stdout aside, point fd 1 at stderr for everything else, and emit the line through _emit().
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def _emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 METRIC = "frame_iters_per_sec"
 UNIT = "frame-iters/s"
 V, J, NE, NB, KC = 6890, 24, 21, 10, 217
@@ -126,7 +137,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": wall,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -336,7 +347,7 @@ def run_fit(args, rank, world, local, dev):
             "gpu_launches": int(sum(v[1] for v in (prof_ch or {}).values()) + sum(v[1] for v in (prof_mk or {}).values())),
             "roofline": roofline, "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -554,7 +565,7 @@ def main():
             "gpu_launches": launches_per_step * args.steps, "roofline": roofline,
             "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
