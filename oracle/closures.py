@@ -153,6 +153,20 @@ def part_fit_loss(smpl: OracleSMPL, markers_subset, pose_body, betas, o_betas, r
     return loss
 
 
+def chamfer_distance_by_part(markers, vertices, marker_labels, vertex_weights, single_directional: bool = False):
+    """src/video_mocap/optimization.py:682-700 ("part_chamfer")."""
+    vertex_mask = torch.argmax(vertex_weights, dim=-1)
+    marker_labels_mode = torch.mode(marker_labels, dim=0)[0]
+    loss = 0
+    for i in torch.unique(marker_labels_mode).tolist():
+        vertices_part = vertices[:, vertex_mask == i]
+        markers_part = markers[:, marker_labels_mode == i]
+        loss_part = (p3d.chamfer_distance(vertices_part, markers_part, single_directional=single_directional)[0]
+                     - MARKER_DISTANCE) ** 2
+        loss = loss + loss_part
+    return loss
+
+
 # ------------------------------------------------------------------------------------------
 # optimiser drivers
 # ------------------------------------------------------------------------------------------

@@ -139,3 +139,16 @@ def test_halo_exchange_and_sharded_temporal_gloo(world):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_worker, args=(world, port, 11, 5, out), nprocs=world, join=True)
     assert all(out.get(r) for r in range(world)), dict(out)
+
+
+def test_sub_hierarchies_match_reference_golden():
+    """Candidate sub-trees of the part fits == the reference's get_sub_hierachies (utils/smpl_utils.py:106-160),
+    same sets AND same order; the golden file was produced by the reference's own function
+    (oracle/gen_golden_parts.py)."""
+    import json
+    import os
+    from uuo_mocap_b200.parts import sub_hierarchies
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "sub_hierarchies.json")))
+    for k, ref in g["subtrees"].items():
+        assert sub_hierarchies(g["parents"], int(k)) == ref, k
+    assert sub_hierarchies(g["parents"], 99) == [sorted(range(24))]
