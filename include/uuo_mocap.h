@@ -182,6 +182,20 @@ int uuo_transvel_accumulate(const float* trans, const float* mm, const float* pr
 int uuo_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);
 
+/* ---- evaluation metrics, the step right after the path (src/video_mocap/evaluation/metrics.py) ----
+ * out[0] = mean over frames and selected points of ||a - b||_2 (compute_MPJPE / compute_V2V, :49-62,126-135; sel[n_sel]
+ * = point ids or NULL for all P); velocity != 0: on (x[t+1]-x[t])*freq instead (compute_MPJVE, :65-87).
+ * scratch: 1024 floats of device memory. */
+int uuo_point_error_mean(const float* a, const float* b, int F, int P, const int32_t* sel, int n_sel, int velocity,
+                         float freq, float* scratch, float* out, void* stream);
+/* compute_similarity_transform (:138-190): out[F,N,3] = S1 after the similarity transform (scale, rotation with
+ * det +1, translation) that brings it closest to S2, one 3x3 SVD per frame. */
+int uuo_similarity_transform(const float* S1, const float* S2, int F, int N, float* out, void* stream);
+/* compute_marker_to_surface_distance (:26-46, igl.signed_distance there): dist[F,M] = unsigned distance from every
+ * point to the closest triangle of the frame's mesh; faces[NF,3] int32 shared by all frames. */
+int uuo_point_mesh_distance(const float* points, const float* vertices, const int32_t* faces, int F, int M, int V,
+                            int NF, float* dist, void* stream);
+
 /* ---- measurement aid (bench.py): per-kernel CUDA-event timing on the launching stream.
  * uuo_profile_enable(1) clears and starts recording, (0) stops.  uuo_profile_read(slot, ...) returns the
  * number of slots; for a valid slot it waits for its events and reports the summed duration and count. */

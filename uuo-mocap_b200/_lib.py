@@ -44,6 +44,9 @@ SIGNATURES = {
     "uuo_temporal_accumulate": (_I, [_P, _P, _P, _I, _I, _F, _P, _P, _P]),
     "uuo_marker_mean": (_I, [_P, _I, _I, _P, _P]),
     "uuo_transvel_accumulate": (_I, [_P, _P, _P, _P, _I, _F, _P, _P, _P]),
+    "uuo_point_error_mean": (_I, [_P, _P, _I, _I, _P, _I, _I, _F, _P, _P, _P]),
+    "uuo_similarity_transform": (_I, [_P, _P, _I, _I, _P, _P]),
+    "uuo_point_mesh_distance": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P]),
     "uuo_profile_enable": (_I, [_I]),
     "uuo_profile_read": (_I, [_I, C.c_char_p, _I, C.POINTER(_F), C.POINTER(_I)]),
     "uuo_adam_step": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _I, _P]),
