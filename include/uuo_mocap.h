@@ -182,6 +182,12 @@ int uuo_transvel_accumulate(const float* trans, const float* mm, const float* pr
 int uuo_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);
 
+/* The same update with the step number in DEVICE memory: uses *step_counter + 1 as `step`, then increments the counter
+ * on the stream.  Nothing on the host changes from one iteration to the next, so closure + update can be captured
+ * once in a CUDA graph and replayed (fit.run_adam). */
+int uuo_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                      float beta1, float beta2, float eps, int32_t* step_counter, void* stream);
+
 /* ---- evaluation metrics, the step right after the path (src/video_mocap/evaluation/metrics.py) ----
  * out[0] = mean over frames and selected points of ||a - b||_2 (compute_MPJPE / compute_V2V, :49-62,126-135; sel[n_sel]
  * = point ids or NULL for all P); velocity != 0: on (x[t+1]-x[t])*freq instead (compute_MPJVE, :65-87).

@@ -244,3 +244,36 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
             continue
         for a, b, what in zip(g, outs["dense"], ("betas", "global_orient", "body_pose", "transl")):
             assert rel_err(a.cpu().numpy(), b.cpu().numpy()) < 1e-4, (name, what)
+
+
+def test_adam_graph_replay_equals_eager(ctx):
+    """run_adam: 3 eager iterations + CUDA-graph replays (step number in device memory) == all-eager iterations."""
+    from uuo_mocap_b200 import fit
+    model, smpl, _ = ctx
+    F, iters = 12, 17
+    cap = _setup_fit(ctx, F, seed=33)
+    mk = _T(cap.markers)
+    res = {}
+    for use_graph in (False, True):
+        prob = fit.FitProblem(smpl, mk, _T(cap.prior_pose_body), _T(cap.prior_betas))
+        pb = fit.ParamBlock.build({"trans": _T(cap.prior_trans), "z_angle": torch.zeros(F), "betas": _T(cap.prior_betas),
+                                   "pose_body": _T(cap.prior_pose_body)}, "cuda:0")
+        root = _T(cap.prior_root_orient).cuda()
+        losses = {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0, "trans_vel": 1.0}
+        loss = fit.run_adam(pb, lambda: fit.chamfer_closure(prob, pb, root, losses), iters, 0.01, graph=use_graph)
+        torch.cuda.synchronize()
+        res[use_graph] = (pb.flat.clone(), float(loss), prob.idx.clone())
+    assert torch.equal(res[True][2], res[False][2])
+    assert rel_err(res[True][0].cpu().numpy(), res[False][0].cpu().numpy()) < 1e-6
+    assert abs(res[True][1] - res[False][1]) <= 1e-6 * abs(res[False][1])
+    # and against the host-step entry point
+    from uuo_mocap_b200 import ops
+    p = torch.randn(1000, device="cuda:0"); g = torch.randn(1000, device="cuda:0")
+    s1 = [p.clone(), torch.zeros_like(p), torch.zeros_like(p)]
+    s2 = [p.clone(), torch.zeros_like(p), torch.zeros_like(p)]
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    for it in range(1, 6):
+        ops.adam_step(s1[0], g, s1[1], s1[2], 0.01, it)
+        ops.adam_step_dev(s2[0], g, s2[1], s2[2], 0.01, cnt)
+    assert int(cnt.item()) == 5
+    assert torch.allclose(s1[0], s2[0], rtol=1e-6, atol=1e-7)

@@ -50,6 +50,7 @@ SIGNATURES = {
     "uuo_profile_enable": (_I, [_I]),
     "uuo_profile_read": (_I, [_I, C.c_char_p, _I, C.POINTER(_F), C.POINTER(_I)]),
     "uuo_adam_step": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _I, _P]),
+    "uuo_adam_step_dev": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _P, _P]),
 }
 
 _lib = None

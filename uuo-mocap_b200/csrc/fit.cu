@@ -172,6 +172,31 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// Same update with the step number held in DEVICE memory (read here, incremented by adam_count_kernel right after), so one
+// closure + Adam iteration can be captured once in a CUDA graph and replayed: nothing on the host changes per step.
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ m, float* __restrict__ v, size_t n, float lr,
+                                                       float beta1, float beta2, float eps,
+                                                       const int32_t* __restrict__ step_counter) {
+  __shared__ float s_step_size, s_bc2_sqrt;
+  if (threadIdx.x == 0) {
+    const double step = (double)(*step_counter + 1);
+    s_step_size = (float)((double)lr / (1.0 - pow((double)beta1, step)));
+    s_bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
+  }
+  __syncthreads();
+  const float step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = m[i] + (gi - m[i]) * (1.f - beta1);
+    const float vi = v[i] * beta2 + (1.f - beta2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+__global__ void adam_count_kernel(int32_t* step_counter) { *step_counter += 1; }
+
 static inline int nblocks(size_t n, int cap = 148 * 8) {
   size_t b = (n + 255) / 256;
   return (int)(b < 1 ? 1 : (b > (size_t)cap ? cap : b));
@@ -257,6 +282,18 @@ extern "C" int uuo_adam_step(float* param, const float* grad, float* exp_avg, fl
   ProfScope ps_("adam_step", (cudaStream_t)stream);
   adam_kernel<<<nblocks(n), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, beta1, beta2, eps,
                                                             (float)((double)lr / bc1), (float)sqrt(bc2));
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+extern "C" int uuo_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
+                                 float beta1, float beta2, float eps, int32_t* step_counter, void* stream) {
+  UUO_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && step_counter, "NULL pointer");
+  if (n == 0) return UUO_OK;
+  ProfScope ps_("adam_step", (cudaStream_t)stream);
+  adam_dev_kernel<<<nblocks(n), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
+                                                                step_counter);
+  adam_count_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_counter);
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }

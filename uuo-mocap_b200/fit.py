@@ -249,17 +249,43 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
 # optimiser drivers
 # ------------------------------------------------------------------------------------------------
 def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int, lr: float,
-             betas=(0.9, 0.999), eps: float = 1e-8, on_iter: Optional[Callable] = None) -> Optional[torch.Tensor]:
-    """closure -> fused Adam over the flat block.  No host synchronisation inside the loop unless
-    ``on_iter`` asks for the loss."""
+             betas=(0.9, 0.999), eps: float = 1e-8, on_iter: Optional[Callable] = None,
+             graph: Optional[bool] = None, warm: int = 3) -> Optional[torch.Tensor]:
+    """closure -> fused Adam over the flat block.  No host synchronisation inside the loop unless ``on_iter`` asks
+    for the loss.  After ``warm`` eager iterations ONE iteration (every kernel of the closure + the update, ~20-35
+    launches) is captured in a CUDA graph and replayed for the rest: the step number lives in device memory
+    (uuo_adam_step_dev), so nothing on the host changes between iterations.  ``graph=None``: on unless a callback
+    wants the loss, the per-kernel profiler is running, or the closure talks to other ranks."""
     m = torch.zeros_like(pb.flat)
     v = torch.zeros_like(pb.flat)
+    counter = torch.zeros(1, dtype=torch.int32, device=pb.flat.device)
+    if graph is None:
+        graph = on_iter is None and not ops.PROFILING[0] and not (torch.distributed.is_available()
+                                                                  and torch.distributed.is_initialized())
     loss = None
-    for it in range(1, num_iters + 1):
-        loss = closure()
-        ops.adam_step(pb.flat, pb.grad, m, v, lr, it, betas, eps)
+
+    def one():
+        out = closure()
+        ops.adam_step_dev(pb.flat, pb.grad, m, v, lr, counter, betas, eps)
+        return out
+
+    it = 0
+    eager = num_iters if not graph or num_iters <= warm + 1 else warm
+    for _ in range(eager):
+        loss = one()
+        it += 1
         if on_iter is not None:
             on_iter(it - 1, loss)
+    if it < num_iters:
+        dev = pb.flat.device
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.device(dev):
+            with torch.cuda.graph(g):
+                loss = one()
+            while it < num_iters:        # the capture itself executed nothing
+                g.replay()
+                it += 1
+            torch.cuda.current_stream(dev).synchronize()     # the graph (and its memory pool) dies with this frame
     return loss
 
 

@@ -124,7 +124,24 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, betas=(0.9, 0.999), ep
                                        stream_ptr(param.device)))
 
 
+def adam_step_dev(param, grad, exp_avg, exp_avg_sq, lr, step_counter, betas=(0.9, 0.999), eps=1e-8):
+    """adam_step with the step number in device memory (int32[1], incremented on the stream): graph-capturable."""
+    for t in (param, grad, exp_avg, exp_avg_sq):
+        if not (t.is_cuda and t.is_contiguous() and t.dtype == torch.float32):
+            raise _lib.UuoError("adam_step needs contiguous fp32 CUDA tensors")
+    if not (step_counter.is_cuda and step_counter.dtype == torch.int32 and step_counter.numel() == 1):
+        raise _lib.UuoError("step_counter must be an int32 CUDA tensor with one element")
+    with torch.cuda.device(param.device):
+        check(_lib.lib().uuo_adam_step_dev(ptr(param), ptr(grad), ptr(exp_avg), ptr(exp_avg_sq), param.numel(),
+                                           float(lr), float(betas[0]), float(betas[1]), float(eps), ptr(step_counter),
+                                           stream_ptr(param.device)))
+
+
+PROFILING = [False]
+
+
 def profile_enable(on: bool):
+    PROFILING[0] = bool(on)
     check(_lib.lib().uuo_profile_enable(1 if on else 0))
 
 
