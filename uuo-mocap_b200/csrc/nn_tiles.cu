@@ -361,7 +361,9 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   float* mk = reinterpret_cast<float*>(smem_raw + L.off_mk);
   unsigned* list = reinterpret_cast<unsigned*>(smem_raw + L.off_list);
   __shared__ __align__(8) uint64_t load_bar[2];
-  __shared__ unsigned list_count;
+  __shared__ unsigned list_count;      // pairs reserved so far
+  __shared__ unsigned list_next;       // pairs handed out to consumers so far
+  __shared__ unsigned producers_done;  // warps that have appended all their pairs
   const float INF = __int_as_float(0x7f800000);
   if (tid == 0) {
     umma::mbar_init(umma::smem_u32(&load_bar[0]), 1);
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     const float* src = vertices + (size_t)f * nflt;
     float* stage = stage0 + (size_t)b * L.stage_floats;
     if (hull_ok(f)) {
-      if (tid == 0) {
+      if (tid == NP_THREADS - 32) {          // a warp that builds no boxes (step 2 keeps warps 0..13 busy)
         const uint32_t bar = umma::smem_u32(&load_bar[b]);
         const uintptr_t a = reinterpret_cast<uintptr_t>(src), lo = a & ~(uintptr_t)15;
         const uint32_t bytes = (uint32_t)(((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) - lo);
@@ -409,13 +411,19 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   long long tick_ = clock64();
 #endif
   for (int f = blockIdx.x; f < F; f += gridDim.x, buf ^= 1) {
-    // the other buffer was last read during the previous frame, which ended with a barrier
-    if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
     if (hull_ok(f)) { umma::mbar_wait(umma::smem_u32(&load_bar[buf]), parity[buf]); parity[buf] ^= 1; }
-    else if (f + (int)gridDim.x < F && !hull_ok(f + gridDim.x)) asm volatile("cp.async.wait_group 1;" ::: "memory");
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     NP_TICK(0);   // wait for the frame
+    // the other buffer was last read during the previous frame, which ended with a barrier: stream the next frame in
+    // now, and fetch this frame's markers while the boxes are built (they are first read two barriers from here)
+    if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
+    if (tid >= NP_THREADS / 2) {             // the upper warps have no boxes to build: they fetch the markers
+      for (int i = tid - NP_THREADS / 2; i < min(NP_MAXM, M) * 3; i += NP_THREADS / 2)
+        mk[i] = __ldg(markers + (size_t)f * M * 3 + i);
+      if (tid == NP_THREADS / 2) { list_count = 0; list_next = 0; producers_done = 0; }
+      for (int i = tid - NP_THREADS / 2; i < NP_LIST; i += NP_THREADS / 2) list[i] = 0xffffffffu;   // "not written yet"
+    }
     const float* raw = stage0 + (size_t)buf * L.stage_floats +
                        (int)((reinterpret_cast<uintptr_t>(vertices + (size_t)f * nflt) & 15) >> 2);
     // ---- 2. tile boxes: one lane per HALF tile (16 vertices walked serially), 16 tiles per warp.  Lane l starts its
@@ -455,8 +463,11 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     }
     for (int m0 = 0; m0 < M; m0 += NP_MAXM) {
       const int mc = min(NP_MAXM, M - m0);
-      for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
-      if (tid == 0) list_count = 0;
+      if (m0 > 0) {
+        for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
+        if (tid == 0) { list_count = 0; list_next = 0; producers_done = 0; }
+        for (int i = tid; i < NP_LIST; i += nthr) list[i] = 0xffffffffu;
+      }
       __syncthreads();                                   // round boxes, markers, counter
       NP_TICK(2);
       // ---- 3a. bound + candidate pairs, one warp per marker
@@ -489,6 +500,7 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
           base = __shfl_sync(0xffffffffu, base, 0);
           const unsigned slot = base + __popc(cb & ((1u << lane) - 1u));
           const bool stored = cand && slot < NP_LIST;
+          __threadfence_block();                 // key[m] (initialised above) is visible before the pair that refers to it
           if (stored) list[slot] = ((unsigned)m << 16) | (unsigned)(r * 32 + lane);
           unsigned over = __ballot_sync(0xffffffffu, cand && !stored);           // list full: evaluate here
           while (over) {
@@ -498,16 +510,40 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
           }
         }
       }
-      __syncthreads();
-      NP_TICK(3);   // 3a
+      // this warp has appended all its pairs (writes before the count: a consumer that sees nwarp here sees them all)
+      __syncwarp();
+      if (lane == 0) { __threadfence_block(); atomicAdd(&producers_done, 1u); }
+      NP_TICK(3);   // 3a (no barrier: a warp that is done producing starts draining right away)
       // ---- 3b. drain the pair list: one lane per HALF pair (16 vertices walked serially, rotated start as in step 2:
-      // no bank conflicts whatever the tiles are), 16 pairs per warp; the lane-local lexicographic minimum of
-      // (distance, original id) is merged with one atomicMin
-      const int np = (int)min(list_count, (unsigned)NP_LIST);
-      for (int qb = warp * 16; qb < np; qb += nwarp * 16) {
-        const int q = qb + (lane & 15), rot = lane & 15;
-        if (q < np) {
-          const unsigned e = list[q];
+      // no bank conflicts whatever the tiles are), 16 pairs per warp-step handed out by an atomic cursor; the
+      // lane-local lexicographic minimum of (distance, original id) is merged with one atomicMin.  Pairs may still
+      // be arriving: a lane waits until its slot is reserved (or every producer is done) and then until it is written.
+      for (;;) {
+        unsigned qb = 0;
+        if (lane == 0) qb = atomicAdd(&list_next, 16u);
+        qb = __shfl_sync(0xffffffffu, qb, 0);
+        if (qb >= NP_LIST) break;
+        const unsigned q = qb + (lane & 15);
+        const int rot = lane & 15;
+        bool mine = false;
+        for (unsigned spins = 0;; ++spins) {
+          const bool done = *reinterpret_cast<volatile unsigned*>(&producers_done) == (unsigned)nwarp;
+          const unsigned cnt = min(*reinterpret_cast<volatile unsigned*>(&list_count), (unsigned)NP_LIST);
+          if (q < cnt) { mine = true; break; }
+          if (done) break;                       // cnt was read after done: it is final
+          if (spins > (1u << 26)) __trap();      // a protocol bug must not hang the box
+        }
+        if (!__any_sync(0xffffffffu, mine)) {    // nothing left in [qb, qb+16) and nothing more will come
+          if (*reinterpret_cast<volatile unsigned*>(&producers_done) == (unsigned)nwarp &&
+              qb >= min(*reinterpret_cast<volatile unsigned*>(&list_count), (unsigned)NP_LIST)) break;
+          continue;
+        }
+        if (mine) {
+          unsigned e = *reinterpret_cast<volatile unsigned*>(list + q);
+          for (unsigned spins = 0; e == 0xffffffffu; ++spins) {
+            e = *reinterpret_cast<volatile unsigned*>(list + q);
+            if (spins > (1u << 26)) __trap();
+          }
           const int m = (int)(e >> 16), t = (int)(e & 0xffffu);
           const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
           const int p0 = t * 32 + (lane >> 4) * 16;
