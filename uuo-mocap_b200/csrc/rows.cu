@@ -110,8 +110,9 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32) rows_forward_kernel(
 // Persistent CTAs keep the 3R selected rows of Bt in shared memory (pitch KP+1: conflict-free when lanes
 // walk different rows at the same k), so the blend-shape part is a small GEMM out of shared memory:
 // lanes across the 3R outputs, the frame's coefficients broadcast.  Then one row per lane for the blend.
-#define ROWSS_WARPS 8
+#define ROWSS_WARPS 16
 #define ROWSS_NI 6            // 3R <= 192
+#define ROWSS_NF 2            // frames per warp pass: every Bt value read from shared memory feeds two frames
 
 struct rowss_layout {
   int pitch, n3;
@@ -124,9 +125,9 @@ __host__ __device__ inline rowss_layout rowss_make_layout(int KP, int R, int J) 
   L.off_vt = (size_t)L.n3 * L.pitch * 4;
   L.off_w = L.off_vt + (size_t)((L.n3 + 3) & ~3) * 4;
   L.off_coef = (L.off_w + (size_t)R * J * 4 + 15) & ~(size_t)15;
-  L.off_A = L.off_coef + (size_t)ROWSS_WARPS * ROWS_MAXKP * 4;
-  L.off_vp = L.off_A + (size_t)ROWSS_WARPS * UUO_SKIN_J * 12 * 4;
-  L.total = L.off_vp + (size_t)ROWSS_WARPS * 32 * ROWSS_NI * 4;
+  L.off_A = L.off_coef + (size_t)ROWSS_WARPS * ROWSS_NF * ROWS_MAXKP * 4;
+  L.off_vp = L.off_A + (size_t)ROWSS_WARPS * ROWSS_NF * UUO_SKIN_J * 12 * 4;
+  L.total = L.off_vp + (size_t)ROWSS_WARPS * ROWSS_NF * 32 * ROWSS_NI * 4;
   return L;
 }
 
@@ -140,9 +141,9 @@ __global__ void __launch_bounds__(ROWSS_WARPS * 32, 1) rows_forward_shared_kerne
   float* s_vt = reinterpret_cast<float*>(smem_raw + L.off_vt);         // [3R]
   float* s_W = reinterpret_cast<float*>(smem_raw + L.off_w);           // [R][J]
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  float* s_coef = reinterpret_cast<float*>(smem_raw + L.off_coef) + w * ROWS_MAXKP;
-  float* s_A = reinterpret_cast<float*>(smem_raw + L.off_A) + w * UUO_SKIN_J * 12;
-  float* s_vp = reinterpret_cast<float*>(smem_raw + L.off_vp) + w * 32 * ROWSS_NI;
+  float* s_coef = reinterpret_cast<float*>(smem_raw + L.off_coef) + w * ROWSS_NF * ROWS_MAXKP;     // [NF][KP]
+  float* s_A = reinterpret_cast<float*>(smem_raw + L.off_A) + w * ROWSS_NF * UUO_SKIN_J * 12;      // [NF][J][12]
+  float* s_vp = reinterpret_cast<float*>(smem_raw + L.off_vp) + w * ROWSS_NF * 32 * ROWSS_NI;      // [NF][3R]
   const int n3 = L.n3, pitch = L.pitch;
   for (int i = tid; i < n3 * KP; i += ROWSS_WARPS * 32) {
     const int n = i / KP, k = i - n * KP;
@@ -151,56 +152,72 @@ __global__ void __launch_bounds__(ROWSS_WARPS * 32, 1) rows_forward_shared_kerne
   for (int i = tid; i < n3; i += ROWSS_WARPS * 32) s_vt[i] = vt[3 * rows[i / 3] + i % 3];
   for (int i = tid; i < R * J; i += ROWSS_WARPS * 32) s_W[i] = W[(size_t)rows[i / J] * J + i % J];
   __syncthreads();
-  const float4* s_coef4 = reinterpret_cast<const float4*>(s_coef);
-  const float4* s_A4 = reinterpret_cast<const float4*>(s_A);
-  for (int f = blockIdx.x * ROWSS_WARPS + w; f < F; f += gridDim.x * ROWSS_WARPS) {
-    stage_frame(coef, A, KP, J, f, lane, s_coef, s_A);
+  for (int f0 = (blockIdx.x * ROWSS_WARPS + w) * ROWSS_NF; f0 < F; f0 += gridDim.x * ROWSS_WARPS * ROWSS_NF) {
+#pragma unroll
+    for (int u = 0; u < ROWSS_NF; ++u)       // an odd tail repeats the last frame (computed twice, stored once)
+      stage_frame(coef, A, KP, J, min(f0 + u, F - 1), lane, s_coef + u * ROWS_MAXKP, s_A + u * UUO_SKIN_J * 12);
     // v_posed of the 3R outputs: lane owns n = lane + 32 i
-    float acc[ROWSS_NI];
+    float acc[ROWSS_NF][ROWSS_NI];
     const float* bp[ROWSS_NI];
 #pragma unroll
     for (int i = 0; i < ROWSS_NI; ++i) {
-      acc[i] = 0.f;
+#pragma unroll
+      for (int u = 0; u < ROWSS_NF; ++u) acc[u][i] = 0.f;
       bp[i] = s_B + min(lane + 32 * i, n3 - 1) * pitch;
     }
     for (int k4 = 0; k4 < (KP >> 2); ++k4) {
-      const float4 c = s_coef4[k4];
+      float4 c[ROWSS_NF];
+#pragma unroll
+      for (int u = 0; u < ROWSS_NF; ++u) c[u] = reinterpret_cast<const float4*>(s_coef + u * ROWS_MAXKP)[k4];
 #pragma unroll
       for (int i = 0; i < ROWSS_NI; ++i) {
         if (32 * i < n3) {
           const float* b = bp[i] + 4 * k4;
-          acc[i] = fmaf(c.x, b[0], acc[i]);
-          acc[i] = fmaf(c.y, b[1], acc[i]);
-          acc[i] = fmaf(c.z, b[2], acc[i]);
-          acc[i] = fmaf(c.w, b[3], acc[i]);
+          const float b0 = b[0], b1 = b[1], b2 = b[2], b3 = b[3];
+#pragma unroll
+          for (int u = 0; u < ROWSS_NF; ++u) {
+            acc[u][i] = fmaf(c[u].x, b0, acc[u][i]);
+            acc[u][i] = fmaf(c[u].y, b1, acc[u][i]);
+            acc[u][i] = fmaf(c[u].z, b2, acc[u][i]);
+            acc[u][i] = fmaf(c[u].w, b3, acc[u][i]);
+          }
         }
       }
     }
 #pragma unroll
     for (int i = 0; i < ROWSS_NI; ++i) {
       const int n = lane + 32 * i;
-      if (n < n3) s_vp[n] = acc[i] + s_vt[n];
+      if (n < n3) {
+#pragma unroll
+        for (int u = 0; u < ROWSS_NF; ++u) s_vp[u * 32 * ROWSS_NI + n] = acc[u][i] + s_vt[n];
+      }
     }
     __syncwarp();
-    float tr[3] = {0.f, 0.f, 0.f};
-    if (transl) { tr[0] = transl[(size_t)f * 3]; tr[1] = transl[(size_t)f * 3 + 1]; tr[2] = transl[(size_t)f * 3 + 2]; }
-    for (int r = lane; r < R; r += 32) {
-      const float vp0 = s_vp[3 * r], vp1 = s_vp[3 * r + 1], vp2 = s_vp[3 * r + 2];
-      if (rowbuf) reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(vp0, vp1, vp2, 0.f);
-      float T[12];
+    for (int u = 0; u < ROWSS_NF; ++u) {
+      const int f = f0 + u;
+      if (f >= F) break;
+      const float4* s_A4 = reinterpret_cast<const float4*>(s_A + u * UUO_SKIN_J * 12);
+      const float* vpu = s_vp + u * 32 * ROWSS_NI;
+      float tr[3] = {0.f, 0.f, 0.f};
+      if (transl) { tr[0] = transl[(size_t)f * 3]; tr[1] = transl[(size_t)f * 3 + 1]; tr[2] = transl[(size_t)f * 3 + 2]; }
+      for (int r = lane; r < R; r += 32) {
+        const float vp0 = vpu[3 * r], vp1 = vpu[3 * r + 1], vp2 = vpu[3 * r + 2];
+        if (rowbuf) reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(vp0, vp1, vp2, 0.f);
+        float T[12];
 #pragma unroll
-      for (int i = 0; i < 12; ++i) T[i] = 0.f;
-      for (int j = 0; j < J; ++j) {
-        const float wj = s_W[r * J + j];
-        const float4 r0 = s_A4[j * 3], r1 = s_A4[j * 3 + 1], r2 = s_A4[j * 3 + 2];
-        T[0] = fmaf(wj, r0.x, T[0]); T[1] = fmaf(wj, r0.y, T[1]); T[2] = fmaf(wj, r0.z, T[2]); T[3] = fmaf(wj, r0.w, T[3]);
-        T[4] = fmaf(wj, r1.x, T[4]); T[5] = fmaf(wj, r1.y, T[5]); T[6] = fmaf(wj, r1.z, T[6]); T[7] = fmaf(wj, r1.w, T[7]);
-        T[8] = fmaf(wj, r2.x, T[8]); T[9] = fmaf(wj, r2.y, T[9]); T[10] = fmaf(wj, r2.z, T[10]); T[11] = fmaf(wj, r2.w, T[11]);
+        for (int i = 0; i < 12; ++i) T[i] = 0.f;
+        for (int j = 0; j < J; ++j) {
+          const float wj = s_W[r * J + j];
+          const float4 r0 = s_A4[j * 3], r1 = s_A4[j * 3 + 1], r2 = s_A4[j * 3 + 2];
+          T[0] = fmaf(wj, r0.x, T[0]); T[1] = fmaf(wj, r0.y, T[1]); T[2] = fmaf(wj, r0.z, T[2]); T[3] = fmaf(wj, r0.w, T[3]);
+          T[4] = fmaf(wj, r1.x, T[4]); T[5] = fmaf(wj, r1.y, T[5]); T[6] = fmaf(wj, r1.z, T[6]); T[7] = fmaf(wj, r1.w, T[7]);
+          T[8] = fmaf(wj, r2.x, T[8]); T[9] = fmaf(wj, r2.y, T[9]); T[10] = fmaf(wj, r2.z, T[10]); T[11] = fmaf(wj, r2.w, T[11]);
+        }
+        float* o = out_rows + ((size_t)f * R + r) * 3;
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+          o[a] = fmaf(T[a * 4], vp0, fmaf(T[a * 4 + 1], vp1, fmaf(T[a * 4 + 2], vp2, T[a * 4 + 3]))) + tr[a];
       }
-      float* o = out_rows + ((size_t)f * R + r) * 3;
-#pragma unroll
-      for (int a = 0; a < 3; ++a)
-        o[a] = fmaf(T[a * 4], vp0, fmaf(T[a * 4 + 1], vp1, fmaf(T[a * 4 + 2], vp2, T[a * 4 + 3]))) + tr[a];
     }
     __syncwarp();
   }
@@ -340,7 +357,7 @@ int launch_rows_forward(const uuo_model* m, const float* transl, int F, const in
       UUO_CUDA(cudaGetDevice(&dev));
       UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     }
-    const int need = (F + ROWSS_WARPS - 1) / ROWSS_WARPS;
+    const int need = (F + ROWSS_WARPS * ROWSS_NF - 1) / (ROWSS_WARPS * ROWSS_NF);
     rows_forward_shared_kernel<<<need < n_sm ? need : n_sm, ROWSS_WARPS * 32, L.total, st>>>(
         m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows, R, out_rows, rowbuf);
   } else {
