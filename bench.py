@@ -10,6 +10,7 @@ One "step" = one pass of lbs() forward + backward over a batch of F synthetic fr
           copied in and the parameter gradients + a scalar copied out inside the timed region
   roofline : dominant kernel of the step, timed live with CUDA events inside the library
   cpu_baseline : the oracle (bit-identical restatement of the vendored smplx) on the host cores, bounded sample
+  torch_gpu_baseline : the same oracle ops on the B200 through stock PyTorch CUDA kernels (SURVEY.md 8(d) "composition" bar)
 `--impl reference` times that CPU path alone with the same JSON contract.
 """
 from __future__ import annotations
@@ -113,6 +114,35 @@ def cpu_oracle_rate(frames: int, reps: int, threads: int):
             times.append(dt)
     med = float(np.median(times))
     return frames / med, med
+
+
+def torch_gpu_oracle_rate(frames: int, reps: int, dev, seed: int):
+    """SURVEY.md section 8(d) "composition" bar: the oracle's lbs() forward+backward (the reference's own sequence of
+    torch ops) on the B200 through stock PyTorch CUDA kernels (ATen + cuBLAS, fp32, TF32 off like the reference).
+    A reported comparison only -- nothing of the product path runs here.  -> (frame-iters/s, ms per step)."""
+    import uuo_mocap_b200  # noqa: F401
+    from uuo_mocap_b200 import synthetic
+    from oracle.smpl_oracle import OracleSMPL
+    orc = OracleSMPL.from_model(synthetic.make_model("dense")).to(dev)
+    mb = synthetic.make_lbs_microbench(frames, seed=seed)
+    T = lambda k: torch.from_numpy(mb[k]).to(dev)
+    rot0, betas0, tr0, gv, gj = T("rot"), T("betas"), T("transl"), T("g_vertices"), T("g_joints")
+
+    def step():
+        rot, betas, transl = (x.clone().requires_grad_(True) for x in (rot0, betas0, tr0))
+        o = orc.forward(betas, rot[:, 1:], rot[:, :1], transl, pose2rot=False)
+        torch.autograd.backward([o.vertices, o.joints], [gv, gj])
+    for _ in range(3):
+        step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return frames / (ms * 1e-3), ms
 
 
 def run_reference(args, rank, world):
@@ -316,6 +346,7 @@ def run_fit(args, rank, world, local, dev):
             "vposed_gemm": ("tensor", 2.0 * F * KC * 3 * Vn),
             "skin_forward": ("hbm", F * (2 * 3 * Vn * 4 + J * 48 + 12)),
             "nn_argmin_tiles": ("hbm", F * (3 * Vn * 4 + M * 12 + M * 8)),
+            "nn_argmin_presorted": ("hbm", F * (3 * Vn * 4 + M * 12 + M * 12)),
             "nn_argmin": ("hbm", F * (3 * Vn * 4 + M * 12 + M * 8)),
             "rows_forward": ("hbm", F * (KC * 4 + J * 48 + M * 12)),
             "rows_backward": ("hbm", F * (KC * 4 + J * 48 + M * 12 + 292 * 4 + 224 * 4)),
@@ -323,6 +354,9 @@ def run_fit(args, rank, world, local, dev):
             "fk_backward": ("hbm", F * (2 * 916 + 292 * 4 + 224 * 4)),
             "adam_step": ("hbm", pb_ch.flat.numel() * 4 * 7),
         }
+        tp = os.path.join(ROOT, "profiles", "traffic.json")       # ncu DRAM bytes per launch, captured at F = 5000
+        traffic = json.load(open(tp)) if os.path.exists(tp) else {}
+
         def dominant(prof, ms):
             if not prof:
                 return None
@@ -337,11 +371,11 @@ def run_fit(args, rank, world, local, dev):
                 else:
                     ach, peak, unit = work / dur / 1e12, peaks["bf16"] / 2.0, "TFLOP/s"
                 out.update({"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
-                            "peak_source": peaks["src"]})
+                            "peak_source": peaks["src"], "traffic": traffic.get(dom) if F == 5000 else None})
             return out
         r_ch, r_mk = dominant(prof_ch, own_ch), dominant(prof_mk, own_mk)
         roofline = dict(r_ch or {})
-        roofline["traffic"] = None
+        roofline.setdefault("traffic", None)
         roofline["marker_stage"] = r_mk
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -556,7 +590,7 @@ def main():
             traffic = None
             tp = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tp):
-                traffic = json.load(open(tp)).get(dom)
+                traffic = json.load(open(tp)).get(dom) if F == 4096 else None   # captured at F = 4096
             if bound == "hbm":
                 ach, peak, unit = work / dur / 1e9, peaks["hbm"], "GB/s"
             else:
@@ -572,6 +606,16 @@ def main():
             rate, sec = cpu_oracle_rate(args.ref_frames, 3, threads)
             cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                    "sample": "%d of %d frames, 3 timed reps after 1 warm-up, torch threads=%d" % (args.ref_frames, F, threads)}
+        tg = None
+        if world == 1 and not args.no_cpu_baseline:
+            del vertices, joints, ws
+            torch.cuda.empty_cache()
+            try:
+                rate, tms = torch_gpu_oracle_rate(F, 10, dev, 2 + rank)
+                tg = {"value": rate, "unit": UNIT, "ms_per_step": tms, "frames": F,
+                      "kind": "oracle lbs() forward+backward through stock PyTorch CUDA ops (fp32, TF32 off), same inputs"}
+            except Exception as e:   # a reported bar, never a reason to lose the bench line
+                tg = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:120])}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -580,7 +624,7 @@ def main():
                        "l2": "inputs larger than L2 (>= 680 MB streamed per step)"},
             "clocks": clocks, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": launches_per_step * args.steps, "roofline": roofline,
-            "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu,
+            "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
         }
         _emit(line)
     if world > 1:

@@ -153,6 +153,37 @@ def part_fit_loss(smpl: OracleSMPL, markers_subset, pose_body, betas, o_betas, r
     return loss
 
 
+def root_stage_loss(smpl: OracleSMPL, markers, pose_body, betas, root_orient, trans, z_angle, marker_labels,
+                    stage: Dict, chunk: int = 256):
+    """src/video_mocap/optimization.py:57-117 (closure_stage_translation of optim_root).  ``stage`` is
+    config["stages"]["root"].  The "reg_betas" term there reads an undefined ``o_betas`` (NameError) and the
+    "ground" term stops in pdb, so neither is restated."""
+    Fn = pose_body.shape[0]
+    if stage.get("constrained_rotation", False):                                    # :61-62
+        z_root = p3d.compute_root_orient_z(torch.repeat_interleave(z_angle, repeats=Fn, dim=0)) @ root_orient
+    elif stage.get("yaw_lock", False):                                              # :63-64
+        z_root = p3d.compute_root_orient_z(z_angle) @ root_orient
+    else:                                                                           # :65-66
+        z_root = p3d.normalize_rot(z_angle)
+    losses = stage["losses"]
+    verts, _ = _smpl_chunked(smpl, pose_body, torch.repeat_interleave(betas, dim=0, repeats=Fn), z_root, trans, chunk)
+    loss = 0
+    if "part_chamfer" in losses:                                                    # :88-96
+        loss = loss + chamfer_distance_by_part(markers, verts, marker_labels, smpl.lbs_weights,
+                                               single_directional=stage["single_directional"]) * losses["part_chamfer"]
+    if "full_chamfer" in losses:                                                    # :97-104
+        loss = loss + p3d.weighted_chamfer_distance(markers, verts, get_marker_mask(markers).float(),
+                                                    single_directional=stage["single_directional"])[0] * losses["full_chamfer"]
+    if "root_orient_vel" in losses:                                                 # :68-75,105-106
+        vel0 = p3d.so3_relative_angle(p3d.normalize_rot(root_orient[1:, 0]), p3d.normalize_rot(root_orient[:-1, 0]))
+        vel1 = p3d.so3_relative_angle(p3d.normalize_rot(z_root[1:, 0]), p3d.normalize_rot(z_root[:-1, 0]))
+        loss = loss + F.mse_loss(vel1, vel0) * losses["root_orient_vel"]
+    if "trans_vel" in losses:                                                       # :107-111
+        mm = torch.mean(markers, dim=1)
+        loss = loss + F.mse_loss(trans[1:] - trans[:-1], mm[1:] - mm[:-1]) * losses["trans_vel"]
+    return loss
+
+
 def chamfer_distance_by_part(markers, vertices, marker_labels, vertex_weights, single_directional: bool = False):
     """src/video_mocap/optimization.py:682-700 ("part_chamfer")."""
     vertex_mask = torch.argmax(vertex_weights, dim=-1)

@@ -8,6 +8,8 @@ What is below restates the published pytorch3d 0.7.x algorithms:
 * ``pytorch3d.transforms.rotation_conversions``: ``matrix_to_rotation_6d``,
   ``rotation_6d_to_matrix``, ``axis_angle_to_quaternion``, ``quaternion_to_matrix``,
   ``axis_angle_to_matrix``;
+* ``pytorch3d.transforms.so3``: ``so3_relative_angle`` / ``so3_rotation_angle`` (defaults ``cos_angle=False``,
+  ``cos_bound=1e-4``, ``eps=1e-4``) on ``pytorch3d.transforms.math.acos_linear_extrapolation``;
 * ``pytorch3d.ops.knn_points`` (K=1, squared L2, candidates scanned in index order with a
   strict ``<`` so the FIRST minimum wins, distance accumulated as
   ``((dx*dx) + dy*dy) + dz*dz`` in fp32 with separately rounded products, which is what the
@@ -33,6 +35,45 @@ import torch.nn.functional as F
 # ------------------------------------------------------------------------------------------
 # rotation conversions
 # ------------------------------------------------------------------------------------------
+def acos_linear_extrapolation(x: torch.Tensor, bounds: Tuple[float, float]) -> torch.Tensor:
+    """pytorch3d.transforms.math.acos_linear_extrapolation: arccos inside [lo, hi], its first-order Taylor
+    expansion at the bound outside (keeps the gradient finite at +-1)."""
+    import math
+    lo, hi = bounds
+    if lo > hi or lo <= -1.0 or hi >= 1.0:
+        raise ValueError("bad extrapolation bounds")
+    out = torch.empty_like(x)
+    below, above = x <= lo, x >= hi
+    inside = (~below) & (~above)
+    out[inside] = torch.acos(x[inside])
+    taylor = lambda v, x0: math.acos(x0) + (v - x0) * (-1.0 / math.sqrt(1.0 - x0 * x0))
+    out[below] = taylor(x[below], lo)
+    out[above] = taylor(x[above], hi)
+    return out
+
+
+def so3_rotation_angle(R: torch.Tensor, eps: float = 1e-4, cos_angle: bool = False, cos_bound: float = 1e-4):
+    """pytorch3d.transforms.so3.so3_rotation_angle: angle of a batch of rotations from the trace."""
+    if R.dim() != 3 or R.shape[1:] != (3, 3):
+        raise ValueError("Input has to be a batch of 3x3 Tensors.")
+    tr = R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2]
+    if ((tr < -1.0 - eps) + (tr > 3.0 + eps)).any():
+        raise ValueError("A matrix has trace outside valid range [-1-eps,3+eps].")
+    phi_cos = (tr - 1.0) * 0.5
+    if cos_angle:
+        return phi_cos
+    if cos_bound > 0.0:
+        b = 1.0 - cos_bound
+        return acos_linear_extrapolation(phi_cos, (-b, b))
+    return torch.acos(phi_cos)
+
+
+def so3_relative_angle(R1: torch.Tensor, R2: torch.Tensor, cos_angle: bool = False, cos_bound: float = 1e-4,
+                       eps: float = 1e-4) -> torch.Tensor:
+    """pytorch3d.transforms.so3.so3_relative_angle: angle of R1 R2^T (call site optimization.py:66-74)."""
+    return so3_rotation_angle(torch.bmm(R1, R2.permute(0, 2, 1)), eps=eps, cos_angle=cos_angle, cos_bound=cos_bound)
+
+
 def matrix_to_rotation_6d(matrix: torch.Tensor) -> torch.Tensor:
     """First two ROWS of the matrix, flattened."""
     return matrix[..., :2, :].clone().reshape(matrix.shape[:-2] + (6,))

@@ -43,9 +43,9 @@ def rodrigues(rot_vecs: torch.Tensor) -> torch.Tensor:
     c = torch.cos(angle).unsqueeze(1)
     s = torch.sin(angle).unsqueeze(1)
     ax, ay, az = torch.split(axis, 1, dim=1)
-    z = torch.zeros((n, 1), dtype=dtype)
+    z = torch.zeros((n, 1), dtype=dtype, device=rot_vecs.device)
     K = torch.cat([z, -az, ay, az, z, -ax, -ay, ax, z], dim=1).view(n, 3, 3)
-    eye = torch.eye(3, dtype=dtype).unsqueeze(0)
+    eye = torch.eye(3, dtype=dtype, device=rot_vecs.device).unsqueeze(0)
     return eye + s * K + (1 - c) * torch.bmm(K, K)
 
 
@@ -84,6 +84,13 @@ class OracleSMPL:
         self.parents[0] = -1
         self.extra_joint_ids = torch.as_tensor(np.asarray(extra_joint_ids), dtype=torch.long)
 
+    def to(self, device) -> "OracleSMPL":
+        """Same restatement with its constants on ``device`` (bench.py's stock-PyTorch-on-GPU comparison bar;
+        ``parents`` stays on the host, it only drives the Python loop of the chain)."""
+        for name in ("v_template", "shapedirs", "posedirs", "J_regressor", "lbs_weights", "extra_joint_ids"):
+            setattr(self, name, getattr(self, name).to(device))
+        return self
+
     @classmethod
     def from_model(cls, m) -> "OracleSMPL":
         return cls(m.v_template, m.shapedirs, m.posedirs_2d(), m.J_regressor, m.weights, m.parents,
@@ -98,7 +105,7 @@ class OracleSMPL:
         dtype = betas.dtype
         v_shaped = self.v_template + shape_offsets(betas, self.shapedirs)        # lbs.py:209
         J = regress_joints(self.J_regressor, v_shaped)                           # lbs.py:213
-        eye = torch.eye(3, dtype=dtype)
+        eye = torch.eye(3, dtype=dtype, device=betas.device)
         if pose2rot:                                                             # lbs.py:218-225
             R = rodrigues(full_pose.reshape(-1, 3)).view(B, -1, 3, 3)
             feat = (R[:, 1:, :, :] - eye).view(B, -1)
@@ -112,7 +119,7 @@ class OracleSMPL:
         nj = self.J_regressor.shape[0]
         W = self.lbs_weights.unsqueeze(0).expand(B, -1, -1)                      # lbs.py:239
         T = torch.matmul(W, A.view(B, nj, 16)).view(B, -1, 4, 4)                 # lbs.py:242
-        ones = torch.ones([B, v_posed.shape[1], 1], dtype=dtype)
+        ones = torch.ones([B, v_posed.shape[1], 1], dtype=dtype, device=v_posed.device)
         v_h = torch.cat([v_posed, ones], dim=2)
         v_out = torch.matmul(T, v_h.unsqueeze(-1))[:, :, :3, 0]                  # lbs.py:247-250
         extra = torch.index_select(v_out, 1, self.extra_joint_ids)               # vertex_joint_selector.py:74

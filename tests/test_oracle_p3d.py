@@ -136,3 +136,24 @@ def test_closure_golden_reproduced(get_model, golden):
     for got, key in ((pose.grad, "ch_g_pose"), (betas.grad, "ch_g_betas"), (trans.grad, "ch_g_trans"),
                      (z.grad, "ch_g_z")):
         assert np.abs(got.numpy() - g[key]).max() <= 1e-4 * np.abs(g[key]).max(), key
+
+
+def test_so3_relative_angle_vs_scipy_and_extrapolation():
+    """so3_relative_angle (pytorch3d defaults): scipy's geodesic angle inside the bound, the first-order extension of
+    arccos at cos = 1 - 1e-4 above it (finite gradient for identical rotations)."""
+    r1 = Rotation.random(64, random_state=5)
+    r2 = Rotation.random(64, random_state=6)
+    R1, R2 = torch.from_numpy(r1.as_matrix()), torch.from_numpy(r2.as_matrix())
+    got = p3d.so3_relative_angle(R1, R2).numpy()
+    ref = (r1 * r2.inv()).magnitude()
+    inside = np.abs(np.cos(ref)) < 1 - 1e-4
+    assert inside.sum() > 50 and np.abs(got[inside] - ref[inside]).max() < 1e-9
+    same = R1.clone().requires_grad_(True)
+    ang = p3d.so3_relative_angle(same, R1)
+    b = 1.0 - 1e-4
+    expect = np.arccos(b) + (1.0 - b) * (-1.0 / np.sqrt(1.0 - b * b))
+    assert torch.allclose(ang, torch.full_like(ang, expect), atol=1e-9)
+    ang.sum().backward()
+    assert torch.isfinite(same.grad).all()
+    with pytest.raises(ValueError):
+        p3d.so3_relative_angle(2.0 * R1, R1)

@@ -75,6 +75,19 @@ def chamfer_distance(x: torch.Tensor, y: torch.Tensor, weights: Optional[torch.T
     return total, None
 
 
+def weighted_chamfer_distance(x: torch.Tensor, y: torch.Tensor, x_weights: torch.Tensor, model=None):
+    """src/video_mocap/losses/chamfer_distance.py:5-21, differentiable in both clouds: every (frame, marker) is a cloud
+    of one query point against its frame's vertices, weighted by ``x_weights`` [F,M] (the marker mask) and divided
+    by their sum; always single-directional there.  -> (loss, None)."""
+    if not (x.is_cuda and y.is_cuda):
+        raise ops._lib.UuoError("weighted_chamfer_distance needs CUDA tensors (uuo-mocap_b200 has no CPU path)")
+    w = x_weights.to(torch.float32)
+    s = w.sum()
+    if float(s) == 0.0:
+        return x.sum() * 0.0, None
+    return (nearest_sq(x, y, model) * w).sum() / s, None
+
+
 def chamfer_distance_by_part(markers: torch.Tensor, vertices: torch.Tensor, marker_labels: torch.Tensor,
                              vertex_weights: torch.Tensor, single_directional: bool = False) -> torch.Tensor:
     """optimization.py:682-700 ("part_chamfer"): for every body part that owns markers (mode of the per-frame
