@@ -136,6 +136,17 @@ int uuo_model_vertex_order_host(const uuo_model* m, int32_t* out);
  * NULL) receives the winning position, i.e. the row of `vertices` that holds the matched vertex. */
 int uuo_nn_argmin_presorted(const float* markers, const float* vertices, const int32_t* ids, int F, int M, int V,
                             float* dist2, int32_t* idx, int32_t* pos, void* stream);
+/* The same search as the fitting loop runs it, iteration after iteration (weighted_chamfer_distance,
+ * losses/chamfer_distance.py:5-21, inside closure_stage_chamfer, optimization.py:232-239).  Both extras may be NULL.
+ *   weights[F,M]: the per-marker chamfer weights (the marker mask).  A marker whose weight is exactly 0 multiplies
+ *     its distance by 0 in the loss and in every gradient, so it is not searched: dist2 = 0, pos = 0, idx = ids[0].
+ *   hint[F,M]: any guess of pos[F,M], normally the previous iteration's output (hint == pos is allowed: the same
+ *     buffer in and out).  The tile of the hinted row is evaluated first, which tightens the pruning bound; values
+ *     outside [0,V) are ignored.  The outputs never depend on the hint.
+ * Every marker of non-zero weight gets exactly the outputs of uuo_nn_argmin_presorted. */
+int uuo_nn_argmin_presorted_fit(const float* markers, const float* vertices, const int32_t* ids, const float* weights,
+                                const int32_t* hint, int F, int M, int V, float* dist2, int32_t* idx, int32_t* pos,
+                                void* stream);
 
 /* get_marker_mask (optimization.py:703-715): mask[F,M] = (|x|+|y|+|z| != 0) as float 0/1. */
 int uuo_marker_mask(const float* markers, int n_markers_total, float* mask, void* stream);

@@ -154,6 +154,50 @@ def test_nn_argmin_presorted_bit_exact(F, M, V, ties, with_ids):
     assert torch.equal(d.cpu(), d_ref)
 
 
+@pytest.mark.parametrize("F,M,V", [(5, 45, 6890), (3, 300, 515), (150, 45, 6890)])
+@pytest.mark.parametrize("hint_kind", [None, "good", "garbage"])
+def test_nn_argmin_presorted_fit_weights_and_hints(F, M, V, hint_kind):
+    """uuo_nn_argmin_presorted_fit: weight-0 markers report (0, ids[0], 0), every other marker is bit-exact whatever
+    the hint says (the true positions, or garbage incl. out-of-range values), and the weighted chamfer sum
+    sum(w d) / sum(w) is unchanged."""
+    from uuo_mocap_b200 import ops
+    from oracle import p3d_oracle as p3d
+    m, v = _clouds(F, M, V, seed=F + M + V, ties=True)
+    rng = np.random.default_rng(F * 7 + M)
+    w = torch.from_numpy((rng.uniform(size=(F, M)) > 0.3).astype(np.float32) * rng.uniform(0.5, 2.0, size=(F, M)).astype(np.float32))
+    w[0] = 0.0                                         # a frame with every marker dropped
+    m[w == 0] = 0.0                                    # dropped markers sit at the origin like the reference's
+    perm = rng.permutation(V)
+    ids = torch.from_numpy(perm.astype(np.int32)).cuda()
+    d_ref, i_ref = p3d.knn_k1(m, v)
+    hint = None
+    if hint_kind == "good":
+        hint = ops.nn_argmin_presorted(m.cuda(), v[:, perm].contiguous().cuda(), ids, want_pos=True)[2]
+    elif hint_kind == "garbage":
+        hint = torch.from_numpy(rng.integers(-5, V + 40, size=(F, M)).astype(np.int32)).cuda()
+        hint[-1] = 2 ** 31 - 1
+    d, i, p = ops.nn_argmin_presorted(m.cuda(), v[:, perm].contiguous().cuda(), ids, want_pos=True, weights=w.cuda(),
+                                      hint=hint)
+    if hint_kind == "good":          # in == out: the hint buffer is also the pos output
+        d2, i2 = torch.empty_like(d), torch.empty_like(i)
+        from uuo_mocap_b200 import _lib
+        from uuo_mocap_b200._lib import check, ptr, stream_ptr
+        mc, vc, wc = m.cuda(), v[:, perm].contiguous().cuda(), w.cuda()
+        check(_lib.lib().uuo_nn_argmin_presorted_fit(ptr(mc), ptr(vc), ptr(ids), ptr(wc), ptr(hint), F, M, V, ptr(d2), ptr(i2),
+                                                     ptr(hint), stream_ptr(mc.device)))
+        assert torch.equal(d2, d) and torch.equal(i2, i) and torch.equal(hint, p)
+        # and without weights: plain outputs
+        d3, i3 = ops.nn_argmin_presorted(mc, vc, ids, hint=hint)
+        d4, i4 = ops.nn_argmin_presorted(mc, vc, ids)
+        assert torch.equal(d3, d4) and torch.equal(i3, i4)
+    d, i, p = d.cpu(), i.cpu().long(), p.cpu().long()
+    on = w != 0
+    assert torch.equal(d[on], d_ref[on]) and torch.equal(i[on], i_ref[on])
+    assert torch.equal(torch.from_numpy(perm)[p[on]], i[on])
+    assert bool((d[~on] == 0).all()) and bool((p[~on] == 0).all()) and bool((i[~on] == int(perm[0])).all())
+    assert float((d * w).sum() / w.sum()) == float((d_ref * w).sum() / w.sum())
+
+
 def test_visiting_twin_matches_model(get_model):
     """The twin's vertices are the model's vertices renumbered; joints identical; presorted NN on the twin ==
     exhaustive NN on the model (4-byte aligned vertex pointer included)."""

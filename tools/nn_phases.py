@@ -1,6 +1,7 @@
 """Per-phase cycle breakdown of the presorted correspondence kernel (CTA 0).  Needs a library built with
     UUO_EXTRA_NVCC_FLAGS=-DNP_TIMING python -m uuo_mocap_b200.build --force
-then: python tools/nn_phases.py [frames]"""
+then: python tools/nn_phases.py [frames] [gt|prior] [mask] [hint]      (prior: body at the video prior, where the fit starts;
+mask: weight-0 markers skipped through uuo_nn_argmin_presorted_weighted)"""
 import ctypes as C
 import os
 import sys
@@ -18,17 +19,25 @@ model = synthetic.make_model("top4")
 smpl = SMPL(_as_struct(model), device="cuda:0")
 twin = smpl.visiting_twin()
 cap = synthetic.make_capture(model, F, num_markers=41, seed=3, n_ghost=4, dropout_p=0.05, noise_std=0.002)
-rot = torch.from_numpy(synthetic.axis_angle_to_matrix_np(cap.gt_pose_aa.astype(np.float64)).astype(np.float32)).cuda()
-out = twin(betas=torch.from_numpy(cap.gt_betas).cuda(), body_pose=rot[:, 1:], global_orient=rot[:, :1],
-           transl=torch.from_numpy(cap.gt_trans).cuda(), pose2rot=False)
+if "prior" in sys.argv[2:]:
+    rot = torch.cat([torch.from_numpy(cap.prior_root_orient), torch.from_numpy(cap.prior_pose_body)], 1).cuda()
+    betas, transl = torch.from_numpy(cap.prior_betas).cuda(), torch.from_numpy(cap.prior_trans).cuda()
+else:
+    rot = torch.from_numpy(synthetic.axis_angle_to_matrix_np(cap.gt_pose_aa.astype(np.float64)).astype(np.float32)).cuda()
+    betas, transl = torch.from_numpy(cap.gt_betas).cuda(), torch.from_numpy(cap.gt_trans).cuda()
+out = twin(betas=betas, body_pose=rot[:, 1:], global_orient=rot[:, :1], transl=transl, pose2rot=False)
 v = out.vertices.detach().contiguous()
 mk = torch.from_numpy(cap.markers).cuda()
+wts = ops.get_marker_mask(mk) if "mask" in sys.argv[2:] else None
+hint = None
+if "hint" in sys.argv[2:]:      # the previous iteration's matches: here the matches of the same vertices moved by 2 mm
+    hint = ops.nn_argmin_presorted(mk, v + 0.002 * torch.randn_like(v[:, :1]), twin.visit_ids, want_pos=True)[2]
 L = C.CDLL(_lib.LIB_PATH)
 for _ in range(3):
-    ops.nn_argmin_presorted(mk, v, twin.visit_ids)
+    ops.nn_argmin_presorted(mk, v, twin.visit_ids, weights=wts, hint=hint)
 torch.cuda.synchronize()
 L.uuo_debug_nn_phases(None, 1)
-ops.nn_argmin_presorted(mk, v, twin.visit_ids)
+ops.nn_argmin_presorted(mk, v, twin.visit_ids, weights=wts, hint=hint)
 torch.cuda.synchronize()
 buf = (C.c_ulonglong * 8)()
 L.uuo_debug_nn_phases(buf, 0)

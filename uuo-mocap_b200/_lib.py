@@ -35,6 +35,7 @@ SIGNATURES = {
     "uuo_model_vertex_order": (_P, [_P]),
     "uuo_model_vertex_order_host": (_I, [_P, _P]),
     "uuo_nn_argmin_presorted": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P, _P]),
+    "uuo_nn_argmin_presorted_fit": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P]),
     "uuo_marker_mask": (_I, [_P, _I, _P, _P]),
     "uuo_chamfer_rows": (_I, [_P, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
     "uuo_marker_loss_rows": (_I, [_P, _P, _P, _I, _F, _F, _P, _P, _P]),

@@ -304,7 +304,7 @@ extern "C" int uuo_debug_nn_phases(unsigned long long* out, int reset) {
 
 struct np_layout {
   int nr, ntp, stage_floats;
-  size_t off_box, off_rbox, off_key, off_mk, off_list, total;
+  size_t off_box, off_rbox, off_key, off_mk, off_mw, off_mh, off_list, total;
 };
 __host__ __device__ inline np_layout np_make_layout(int V) {
   np_layout L;
@@ -316,7 +316,9 @@ __host__ __device__ inline np_layout np_make_layout(int V) {
   L.off_rbox = L.off_box + (size_t)6 * L.ntp * 4;
   L.off_key = L.off_rbox + 6 * 32 * 4;
   L.off_mk = L.off_key + NP_MAXM * 8;
-  L.off_list = L.off_mk + NP_MAXM * 3 * 4;
+  L.off_mw = L.off_mk + NP_MAXM * 3 * 4;
+  L.off_mh = L.off_mw + NP_MAXM * 4;
+  L.off_list = L.off_mh + NP_MAXM * 4;
   L.total = L.off_list + NP_LIST * 4;
   return L;
 }
@@ -346,10 +348,12 @@ __device__ __forceinline__ void np_eval_merge(const float* __restrict__ raw, con
 
 __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float* __restrict__ markers,
                                                                      const float* __restrict__ vertices,
-                                                                     const int32_t* __restrict__ ids, int F, int M,
+                                                                     const int32_t* __restrict__ ids,
+                                                                     const float* __restrict__ wts,
+                                                                     const int32_t* hint, int F, int M,
                                                                      int V, float* __restrict__ dist2,
                                                                      int32_t* __restrict__ idx,
-                                                                     int32_t* __restrict__ pos_out) {
+                                                                     int32_t* pos_out) {   // may alias hint
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = NP_THREADS, nwarp = NP_THREADS / 32;
   const np_layout L = np_make_layout(V);
@@ -359,6 +363,8 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   float* rbox = reinterpret_cast<float*>(smem_raw + L.off_rbox);
   unsigned long long* key = reinterpret_cast<unsigned long long*>(smem_raw + L.off_key);
   float* mk = reinterpret_cast<float*>(smem_raw + L.off_mk);
+  float* mw = reinterpret_cast<float*>(smem_raw + L.off_mw);      // marker weights: a marker of weight 0 is not searched
+  int* mh = reinterpret_cast<int*>(smem_raw + L.off_mh);          // hinted tile per marker (-1: none)
   unsigned* list = reinterpret_cast<unsigned*>(smem_raw + L.off_list);
   __shared__ __align__(8) uint64_t load_bar[2];
   __shared__ unsigned list_count;      // pairs reserved so far
@@ -421,6 +427,11 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     if (tid >= NP_THREADS / 2) {             // the upper warps have no boxes to build: they fetch the markers
       for (int i = tid - NP_THREADS / 2; i < min(NP_MAXM, M) * 3; i += NP_THREADS / 2)
         mk[i] = __ldg(markers + (size_t)f * M * 3 + i);
+      for (int i = tid - NP_THREADS / 2; i < min(NP_MAXM, M); i += NP_THREADS / 2) {
+        mw[i] = wts ? __ldg(wts + (size_t)f * M + i) : 1.0f;
+        const int h = hint ? hint[(size_t)f * M + i] : -1;      // a plain load: pos_out may be the same buffer
+        mh[i] = h >= 0 && h < V ? h >> 5 : -1;
+      }
       if (tid == NP_THREADS / 2) { list_count = 0; list_next = 0; producers_done = 0; }
       for (int i = tid - NP_THREADS / 2; i < NP_LIST; i += NP_THREADS / 2) list[i] = 0xffffffffu;   // "not written yet"
     }
@@ -465,6 +476,11 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
       const int mc = min(NP_MAXM, M - m0);
       if (m0 > 0) {
         for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
+        for (int i = tid; i < mc; i += nthr) {
+          mw[i] = wts ? __ldg(wts + (size_t)f * M + m0 + i) : 1.0f;
+          const int h = hint ? hint[(size_t)f * M + m0 + i] : -1;
+          mh[i] = h >= 0 && h < V ? h >> 5 : -1;
+        }
         if (tid == 0) { list_count = 0; list_next = 0; producers_done = 0; }
         for (int i = tid; i < NP_LIST; i += nthr) list[i] = 0xffffffffu;
       }
@@ -472,6 +488,10 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
       NP_TICK(2);
       // ---- 3a. bound + candidate pairs, one warp per marker
       for (int m = warp; m < mc; m += nwarp) {
+        if (mw[m] == 0.0f) {                   // weight 0: contributes nothing to the loss or its gradient
+          if (lane == 0) key[m] = np_pack(0.0f, ids ? __ldg(ids) : 0, 0);
+          continue;
+        }
         const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
         const float rlb = lane < nr ? nt_boxdist(rbox, 32, lane, mx, my, mz) : INF;
         const float rmin = redux_min_f32(rlb);
@@ -484,6 +504,14 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
         if (lane == 0) key[m] = np_pack(INF, 0xffff, 0xffff);
         __syncwarp();
         np_eval_merge(raw, ids, V, r0 * 32 + j0, lane, mx, my, mz, key + m);
+        // the hinted tile (where the previous iteration of the fit found this marker's vertex) nearly always holds
+        // the nearest vertex again: evaluating it first makes best0 tight, so few other tiles survive the bound.
+        // Which tiles are evaluated first never changes the result, only how many pairs are left.
+        const int th = mh[m];
+        if (th >= 0 && th != r0 * 32 + j0) {
+          __syncwarp();
+          np_eval_merge(raw, ids, V, th, lane, mx, my, mz, key + m);
+        }
         __syncwarp();
         const float best0 = __uint_as_float((unsigned)(*reinterpret_cast<volatile unsigned long long*>(key + m) >> 32));
         unsigned pend = __ballot_sync(0xffffffffu, lane < nr && !(rlb > best0));     // NaN bounds are never pruned
@@ -491,7 +519,7 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
           const int r = __ffs(pend) - 1;
           pend &= pend - 1;
           lb = nt_boxdist(box, ntp, r * 32 + lane, mx, my, mz);
-          const bool cand = !(lb > best0) && !(r == r0 && lane == j0);
+          const bool cand = !(lb > best0) && !(r == r0 && lane == j0) && r * 32 + lane != th;
           const unsigned cb = __ballot_sync(0xffffffffu, cand);
           if (!cb) continue;
           const int n = __popc(cb);
@@ -589,8 +617,9 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
-extern "C" int uuo_nn_argmin_presorted(const float* markers, const float* vertices, const int32_t* ids, int F, int M,
-                                       int V, float* dist2, int32_t* idx, int32_t* pos, void* stream) {
+static int nn_presorted_launch(const float* markers, const float* vertices, const int32_t* ids, const float* weights,
+                               const int32_t* hint, int F, int M, int V, float* dist2, int32_t* idx, int32_t* pos,
+                               void* stream) {
   UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
   UUO_CHECK_ARG(F >= 0 && M >= 0 && V > 0, "bad sizes");
   const np_layout L = np_make_layout(V);
@@ -610,9 +639,20 @@ extern "C" int uuo_nn_argmin_presorted(const float* markers, const float* vertic
   }
   {
     ProfScope ps_("nn_argmin_presorted", (cudaStream_t)stream);
-    nn_presorted_kernel<<<F < n_sm ? F : n_sm, NP_THREADS, L.total, (cudaStream_t)stream>>>(markers, vertices, ids, F, M, V,
-                                                                                          dist2, idx, pos);
+    nn_presorted_kernel<<<F < n_sm ? F : n_sm, NP_THREADS, L.total, (cudaStream_t)stream>>>(markers, vertices, ids, weights,
+                                                                                          hint, F, M, V, dist2, idx, pos);
   }
   UUO_LAUNCH_CHECK();
   return UUO_OK;
+}
+
+extern "C" int uuo_nn_argmin_presorted(const float* markers, const float* vertices, const int32_t* ids, int F, int M,
+                                       int V, float* dist2, int32_t* idx, int32_t* pos, void* stream) {
+  return nn_presorted_launch(markers, vertices, ids, nullptr, nullptr, F, M, V, dist2, idx, pos, stream);
+}
+
+extern "C" int uuo_nn_argmin_presorted_fit(const float* markers, const float* vertices, const int32_t* ids,
+                                           const float* weights, const int32_t* hint, int F, int M, int V, float* dist2,
+                                           int32_t* idx, int32_t* pos, void* stream) {
+  return nn_presorted_launch(markers, vertices, ids, weights, hint, F, M, V, dist2, idx, pos, stream);
 }

@@ -64,7 +64,7 @@ class FitProblem:
         # see SMPL.visiting_twin); idx holds ORIGINAL vertex ids, pos the matching row of `vertices`
         self.twin = self.smpl.visiting_twin()
         self.idx = torch.empty((self.F, self.M), dtype=torch.int32, device=dev)
-        self.pos = torch.empty((self.F, self.M), dtype=torch.int32, device=dev)
+        self.pos = torch.full((self.F, self.M), -1, dtype=torch.int32, device=dev)   # also the search hint of the next call
         self.d2 = torch.empty((self.F, self.M), dtype=torch.float32, device=dev)
         self.g_rows = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
         self.virt = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
@@ -171,8 +171,11 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
         verts = prob.lbs_forward(brows, root_orient, v["pose_body"], v["z_angle"], v["trans"])
         w_ch = float(losses.get("full_chamfer", 0.0))
         if w_ch != 0.0 and prob.wsum_global > 0:
-            check(_lib.lib().uuo_nn_argmin_presorted(ptr(prob.markers), ptr(verts), ptr(prob.twin.visit_ids), F, M,
-                                                     prob.mh.V, ptr(prob.d2), ptr(prob.idx), ptr(prob.pos), prob._st()))
+            # dropped markers (mask 0) weigh nothing in the loss or the gradient: the kernel does not search them;
+            # prob.pos still holds the previous iteration's matches: the kernel starts its search there (in == out)
+            check(_lib.lib().uuo_nn_argmin_presorted_fit(ptr(prob.markers), ptr(verts), ptr(prob.twin.visit_ids),
+                                                         ptr(prob.mask), ptr(prob.pos), F, M, prob.mh.V, ptr(prob.d2),
+                                                         ptr(prob.idx), ptr(prob.pos), prob._st()))
             check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.pos), F, M,
                                               prob.mh.V, w_ch / prob.wsum_global, ptr(prob.red[15:]), ptr(prob.g_rows),
                                               prob._st()))

@@ -53,9 +53,13 @@ def nn_argmin(markers: torch.Tensor, vertices: torch.Tensor, model=None,
 
 
 def nn_argmin_presorted(markers: torch.Tensor, vertices: torch.Tensor, ids: Optional[torch.Tensor] = None,
-                        want_pos: bool = False):
+                        want_pos: bool = False, weights: Optional[torch.Tensor] = None,
+                        hint: Optional[torch.Tensor] = None):
     """uuo_nn_argmin_presorted: ``vertices`` [F,V,3] already lie in visiting order (a twin model's output),
-    ``ids`` [V] int32 gives the original id of every row.  Returns (dist2, idx) or (dist2, idx, pos)."""
+    ``ids`` [V] int32 gives the original id of every row.  Returns (dist2, idx) or (dist2, idx, pos).
+    With ``weights`` [F,M] and/or ``hint`` [F,M] int32 (uuo_nn_argmin_presorted_fit): markers of weight 0 are not
+    searched and report (0, ids[0], 0) -- they multiply by 0 in weighted_chamfer_distance and in its gradient; the
+    hint (a guess of ``pos``, e.g. the previous iteration's) only tightens the pruning, never changes the outputs."""
     markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
     F, M, _ = markers.shape
     V = vertices.shape[1]
@@ -68,8 +72,19 @@ def nn_argmin_presorted(markers: torch.Tensor, vertices: torch.Tensor, ids: Opti
     i = torch.empty((F, M), dtype=torch.int32, device=dev)
     p = torch.empty((F, M), dtype=torch.int32, device=dev) if want_pos else None
     with torch.cuda.device(dev):
-        check(_lib.lib().uuo_nn_argmin_presorted(ptr(markers), ptr(vertices), ptr(ids), F, M, V, ptr(d), ptr(i), ptr(p),
-                                                 stream_ptr(dev)))
+        if weights is not None or hint is not None:
+            if weights is not None:
+                weights = _req(weights, "weights")
+                if weights.shape != (F, M):
+                    raise ValueError("weights must be [F, M]")
+            if hint is not None and not (hint.is_cuda and hint.dtype == torch.int32 and hint.shape == (F, M)
+                                         and hint.is_contiguous()):
+                raise ValueError("hint must be a contiguous int32 CUDA tensor [F, M]")
+            check(_lib.lib().uuo_nn_argmin_presorted_fit(ptr(markers), ptr(vertices), ptr(ids), ptr(weights), ptr(hint),
+                                                         F, M, V, ptr(d), ptr(i), ptr(p), stream_ptr(dev)))
+        else:
+            check(_lib.lib().uuo_nn_argmin_presorted(ptr(markers), ptr(vertices), ptr(ids), F, M, V, ptr(d), ptr(i), ptr(p),
+                                                     stream_ptr(dev)))
     return (d, i, p) if want_pos else (d, i)
 
 
