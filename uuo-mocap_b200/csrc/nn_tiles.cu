@@ -269,14 +269,15 @@ extern "C" int uuo_nn_argmin_ordered(const float* markers, const float* vertices
 // nothing is gathered: the staged frame is read with stride-3 words (conflict-free) straight from the
 // staging buffer.  ids[p] = original vertex id of position p (ties break on the ORIGINAL numbering).
 //   - one persistent CTA per SM, 32 warps; frames double-buffered with 1-D bulk copies (cp.async.bulk ->
-//     mbarrier), so the HBM stream of frame f+1 overlaps all of frame f;
-//   - 3a: one warp per marker finds the closest round, the closest tile in it, evaluates that tile (an
-//     exact distance that bounds everything else) and appends every other (marker, tile) pair whose box
-//     bound does not exceed it to a work list in shared memory;
-//   - 3b: all warps drain the list, one lane per half pair (16 vertices walked serially with a rotated start, so the
-//     stride-3 reads of 32 different tiles never collide on a bank), balanced however hard a marker is, merging
-//     with atomicMin on a packed 64-bit key  distance bits | original id | position  -- the lexicographic
-//     minimum the reference's first-minimum scan returns.
+//     mbarrier), the next frame's markers / weights / hints prefetched with cp.async, so the HBM stream of
+//     frame f+1 overlaps all of frame f;
+//   - step 2: tile boxes, one lane per half tile; round boxes = union of 32 tile boxes (CREDUX);
+//   - step 3: markers are handed out to warps one by one.  A warp evaluates a FIRST tile (the hinted one, else the
+//     tile with the smallest bound) -> an exact distance best0 that bounds everything else; then every other tile
+//     whose box bound does not exceed best0 is evaluated by the same warp, one vertex per lane, each lane keeping
+//     its own lexicographic minimum of (distance, original id); ONE warp reduction per marker at the end gives
+//     the reference's first minimum.  (r1g kept a shared (marker, tile) pair list drained by all warps: with a
+//     hint only ~4 tiles per marker survive and the list's atomics, fences and waiting cost more than they saved.)
 // =====================================================================================================
 // per-phase cycle counters of CTA 0 (tools/nn_phases.py): compile with -DNP_TIMING
 #ifdef NP_TIMING
@@ -300,11 +301,10 @@ extern "C" int uuo_debug_nn_phases(unsigned long long* out, int reset) {
 
 #define NP_THREADS 1024
 #define NP_MAXM 256          // markers per pass over a frame
-#define NP_LIST 4096         // (marker, tile) pairs; overflow is evaluated inline by the producing warp
 
 struct np_layout {
   int nr, ntp, stage_floats;
-  size_t off_box, off_rbox, off_key, off_mk, off_mw, off_mh, off_list, total;
+  size_t off_box, off_rbox, off_mk, off_mw, off_mh, off_ids, total;
 };
 __host__ __device__ inline np_layout np_make_layout(int V) {
   np_layout L;
@@ -314,36 +314,12 @@ __host__ __device__ inline np_layout np_make_layout(int V) {
   L.stage_floats = (3 * V + 8 + 3) & ~3;
   L.off_box = (size_t)2 * L.stage_floats * 4;
   L.off_rbox = L.off_box + (size_t)6 * L.ntp * 4;
-  L.off_key = L.off_rbox + 6 * 32 * 4;
-  L.off_mk = L.off_key + NP_MAXM * 8;
-  L.off_mw = L.off_mk + NP_MAXM * 3 * 4;
-  L.off_mh = L.off_mw + NP_MAXM * 4;
-  L.off_list = L.off_mh + NP_MAXM * 4;
-  L.total = L.off_list + NP_LIST * 4;
+  L.off_mk = L.off_rbox + 6 * 32 * 4;                 // two buffers each: this frame's and the next frame's
+  L.off_mw = L.off_mk + 2 * NP_MAXM * 3 * 4;
+  L.off_mh = L.off_mw + 2 * NP_MAXM * 4;
+  L.off_ids = L.off_mh + 2 * NP_MAXM * 4;
+  L.total = L.off_ids + (size_t)L.ntp * 32 * 2;
   return L;
-}
-
-__device__ __forceinline__ unsigned long long np_pack(float d, int id, int pos) {
-  return ((unsigned long long)__float_as_uint(d) << 32) | ((unsigned long long)(unsigned)id << 16) | (unsigned)pos;
-}
-
-// evaluate tile t for a marker and merge into key[m]
-__device__ __forceinline__ void np_eval_merge(const float* __restrict__ raw, const int32_t* __restrict__ ids, int V,
-                                              int t, int lane, float mx, float my, float mz,
-                                              unsigned long long* key) {
-  const int pos = min(t * 32 + lane, V - 1);
-  const float* p = raw + 3 * pos;
-  const float d = nt_sqdist(mx, my, mz, p[0], p[1], p[2]);
-  const float dm = redux_min_f32(d);
-  const unsigned cur = (unsigned)(*reinterpret_cast<volatile unsigned long long*>(key) >> 32);
-  // distances are >= 0: their bit patterns order like the values; inf / NaN never win (the exhaustive scan's
-  // strict '<' against an initial +inf never accepts them either)
-  if (__float_as_uint(dm) < 0x7f800000u && __float_as_uint(dm) <= cur) {
-    const int id = ids ? __ldg(ids + pos) : pos;
-    const unsigned cand = d == dm ? (((unsigned)id << 16) | (unsigned)pos) : 0xffffffffu;
-    const unsigned best = __reduce_min_sync(0xffffffffu, cand);
-    if (lane == 0 && best != 0xffffffffu) atomicMin(key, ((unsigned long long)__float_as_uint(dm) << 32) | best);
-  }
 }
 
 __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float* __restrict__ markers,
@@ -361,15 +337,16 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   float* stage0 = reinterpret_cast<float*>(smem_raw);
   float* box = reinterpret_cast<float*>(smem_raw + L.off_box);
   float* rbox = reinterpret_cast<float*>(smem_raw + L.off_rbox);
-  unsigned long long* key = reinterpret_cast<unsigned long long*>(smem_raw + L.off_key);
-  float* mk = reinterpret_cast<float*>(smem_raw + L.off_mk);
-  float* mw = reinterpret_cast<float*>(smem_raw + L.off_mw);      // marker weights: a marker of weight 0 is not searched
-  int* mh = reinterpret_cast<int*>(smem_raw + L.off_mh);          // hinted tile per marker (-1: none)
-  unsigned* list = reinterpret_cast<unsigned*>(smem_raw + L.off_list);
+  float* mk0 = reinterpret_cast<float*>(smem_raw + L.off_mk);
+  float* mw0 = reinterpret_cast<float*>(smem_raw + L.off_mw);      // marker weights: a marker of weight 0 is not searched
+  int* mh0 = reinterpret_cast<int*>(smem_raw + L.off_mh);          // hinted row per marker
+  unsigned short* ids_s = reinterpret_cast<unsigned short*>(smem_raw + L.off_ids);   // original id of every row
+  for (int i = tid; i < ntp * 32; i += nthr) {
+    const int p = min(i, V - 1);
+    ids_s[i] = (unsigned short)(ids ? __ldg(ids + p) : p);
+  }
   __shared__ __align__(8) uint64_t load_bar[2];
-  __shared__ unsigned list_count;      // pairs reserved so far
-  __shared__ unsigned list_next;       // pairs handed out to consumers so far
-  __shared__ unsigned producers_done;  // warps that have appended all their pairs
+  __shared__ unsigned marker_next;     // markers handed out to warps so far
   const float INF = __int_as_float(0x7f800000);
   if (tid == 0) {
     umma::mbar_init(umma::smem_u32(&load_bar[0]), 1);
@@ -383,11 +360,20 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     return (a & ~(uintptr_t)15) >= vbase && ((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) <= vend;
   };
   // stage frame f into buffer b (see nn_tiles_kernel: bulk copy of the 16 B hull, cp.async for out-of-tensor hulls)
+  // and, with cp.async, the first NP_MAXM markers of that frame with their weights and hints
   auto issue_load = [&](int f, int b) {
+    if (tid >= NP_THREADS / 2) {             // the upper warps build no boxes
+      const int t = tid - NP_THREADS / 2, mc = min(NP_MAXM, M);
+      for (int i = t; i < mc * 3; i += NP_THREADS / 2) cp_async4(mk0 + b * NP_MAXM * 3 + i, markers + (size_t)f * M * 3 + i);
+      if (wts)
+        for (int i = t; i < mc; i += NP_THREADS / 2) cp_async4(mw0 + b * NP_MAXM + i, wts + (size_t)f * M + i);
+      if (hint)
+        for (int i = t; i < mc; i += NP_THREADS / 2) cp_async4(mh0 + b * NP_MAXM + i, hint + (size_t)f * M + i);
+    }
     const float* src = vertices + (size_t)f * nflt;
     float* stage = stage0 + (size_t)b * L.stage_floats;
     if (hull_ok(f)) {
-      if (tid == NP_THREADS - 32) {          // a warp that builds no boxes (step 2 keeps warps 0..13 busy)
+      if (tid == NP_THREADS - 32) {
         const uint32_t bar = umma::smem_u32(&load_bar[b]);
         const uintptr_t a = reinterpret_cast<uintptr_t>(src), lo = a & ~(uintptr_t)15;
         const uint32_t bytes = (uint32_t)(((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) - lo);
@@ -397,16 +383,16 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
         for (uint32_t off = 0; off < bytes; off += chunk)
           umma::bulk_g2s(umma::smem_u32(stage) + off, reinterpret_cast<const void*>(lo + off), min(chunk, bytes - off), bar);
       }
-      return;
+    } else {
+      const int mis = (int)((reinterpret_cast<uintptr_t>(src) & 15) >> 2);
+      float* raw = stage + mis;
+      const int head = min(nflt, (4 - mis) & 3);
+      const int body = (nflt - head) >> 2;
+      const int tail0 = head + 4 * body;
+      if (tid < head) cp_async4(raw + tid, src + tid);
+      for (int i = tid; i < body; i += nthr) cp_async16(raw + head + 4 * i, src + head + 4 * i);
+      if (tid < nflt - tail0) cp_async4(raw + tail0 + tid, src + tail0 + tid);
     }
-    const int mis = (int)((reinterpret_cast<uintptr_t>(src) & 15) >> 2);
-    float* raw = stage + mis;
-    const int head = min(nflt, (4 - mis) & 3);
-    const int body = (nflt - head) >> 2;
-    const int tail0 = head + 4 * body;
-    if (tid < head) cp_async4(raw + tid, src + tid);
-    for (int i = tid; i < body; i += nthr) cp_async16(raw + head + 4 * i, src + head + 4 * i);
-    if (tid < nflt - tail0) cp_async4(raw + tail0 + tid, src + tail0 + tid);
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   uint32_t parity[2] = {0, 0};
@@ -417,26 +403,18 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   long long tick_ = clock64();
 #endif
   for (int f = blockIdx.x; f < F; f += gridDim.x, buf ^= 1) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (hull_ok(f)) { umma::mbar_wait(umma::smem_u32(&load_bar[buf]), parity[buf]); parity[buf] ^= 1; }
-    else asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     NP_TICK(0);   // wait for the frame
-    // the other buffer was last read during the previous frame, which ended with a barrier: stream the next frame in
-    // now, and fetch this frame's markers while the boxes are built (they are first read two barriers from here)
+    // the other buffers were last read during the previous frame, which ended with a barrier: stream the next frame in
     if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
-    if (tid >= NP_THREADS / 2) {             // the upper warps have no boxes to build: they fetch the markers
-      for (int i = tid - NP_THREADS / 2; i < min(NP_MAXM, M) * 3; i += NP_THREADS / 2)
-        mk[i] = __ldg(markers + (size_t)f * M * 3 + i);
-      for (int i = tid - NP_THREADS / 2; i < min(NP_MAXM, M); i += NP_THREADS / 2) {
-        mw[i] = wts ? __ldg(wts + (size_t)f * M + i) : 1.0f;
-        const int h = hint ? hint[(size_t)f * M + i] : -1;      // a plain load: pos_out may be the same buffer
-        mh[i] = h >= 0 && h < V ? h >> 5 : -1;
-      }
-      if (tid == NP_THREADS / 2) { list_count = 0; list_next = 0; producers_done = 0; }
-      for (int i = tid - NP_THREADS / 2; i < NP_LIST; i += NP_THREADS / 2) list[i] = 0xffffffffu;   // "not written yet"
-    }
+    if (tid == 0) marker_next = 0;
     const float* raw = stage0 + (size_t)buf * L.stage_floats +
                        (int)((reinterpret_cast<uintptr_t>(vertices + (size_t)f * nflt) & 15) >> 2);
+    float* mk = mk0 + buf * NP_MAXM * 3;
+    float* mw = mw0 + buf * NP_MAXM;
+    int* mh = mh0 + buf * NP_MAXM;
     // ---- 2. tile boxes: one lane per HALF tile (16 vertices walked serially), 16 tiles per warp.  Lane l starts its
     // walk at vertex (l & 15): at every step the 16 lanes of a half read 16 different residues of 3j mod 32 and the
     // other half sits 48 words = 16 banks further, so the stride-96-word tiles never collide on a bank.
@@ -474,144 +452,97 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     }
     for (int m0 = 0; m0 < M; m0 += NP_MAXM) {
       const int mc = min(NP_MAXM, M - m0);
-      if (m0 > 0) {
+      if (m0 > 0) {                                        // later chunks of a large marker set: fetched in place
         for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
         for (int i = tid; i < mc; i += nthr) {
-          mw[i] = wts ? __ldg(wts + (size_t)f * M + m0 + i) : 1.0f;
-          const int h = hint ? hint[(size_t)f * M + m0 + i] : -1;
-          mh[i] = h >= 0 && h < V ? h >> 5 : -1;
+          if (wts) mw[i] = __ldg(wts + (size_t)f * M + m0 + i);
+          if (hint) mh[i] = hint[(size_t)f * M + m0 + i];   // a plain load: pos_out may be the same buffer
         }
-        if (tid == 0) { list_count = 0; list_next = 0; producers_done = 0; }
-        for (int i = tid; i < NP_LIST; i += nthr) list[i] = 0xffffffffu;
+        if (tid == 0) marker_next = 0;
       }
-      __syncthreads();                                   // round boxes, markers, counter
+      __syncthreads();                                     // round boxes, markers, counter
       NP_TICK(2);
-      // ---- 3a. bound + candidate pairs, one warp per marker
-      for (int m = warp; m < mc; m += nwarp) {
-        if (mw[m] == 0.0f) {                   // weight 0: contributes nothing to the loss or its gradient
-          if (lane == 0) key[m] = np_pack(0.0f, ids ? __ldg(ids) : 0, 0);
+      // ---- 3. markers, handed out one by one (their costs differ a lot)
+      for (;;) {
+        int m = 0;
+        if (lane == 0) m = (int)atomicAdd(&marker_next, 1u);
+        m = __shfl_sync(0xffffffffu, m, 0);
+        if (m >= mc) break;
+        const size_t o = (size_t)f * M + m0 + m;
+        if (wts && mw[m] == 0.0f) {            // weight 0: contributes nothing to the loss or its gradient
+          if (lane == 0) {
+            dist2[o] = 0.0f;
+            idx[o] = ids_s[0];
+            if (pos_out) pos_out[o] = 0;
+          }
           continue;
         }
         const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
         const float rlb = lane < nr ? nt_boxdist(rbox, 32, lane, mx, my, mz) : INF;
-        const float rmin = redux_min_f32(rlb);
-        const unsigned bm = __ballot_sync(0xffffffffu, lane < nr && rlb == rmin);
-        const int r0 = bm ? __ffs(bm) - 1 : 0;
-        float lb = nt_boxdist(box, ntp, r0 * 32 + lane, mx, my, mz);
-        const float tmin = redux_min_f32(lb);
-        const unsigned bt = __ballot_sync(0xffffffffu, lb == tmin);
-        const int j0 = bt ? __ffs(bt) - 1 : 0;
-        if (lane == 0) key[m] = np_pack(INF, 0xffff, 0xffff);
-        __syncwarp();
-        np_eval_merge(raw, ids, V, r0 * 32 + j0, lane, mx, my, mz, key + m);
-        // the hinted tile (where the previous iteration of the fit found this marker's vertex) nearly always holds
-        // the nearest vertex again: evaluating it first makes best0 tight, so few other tiles survive the bound.
-        // Which tiles are evaluated first never changes the result, only how many pairs are left.
-        const int th = mh[m];
-        if (th >= 0 && th != r0 * 32 + j0) {
-          __syncwarp();
-          np_eval_merge(raw, ids, V, th, lane, mx, my, mz, key + m);
+        // the first tile: the hinted one (where the previous iteration of the fit found this marker's vertex: it
+        // nearly always holds the nearest vertex again, so best0 is tight and few other tiles survive the bound),
+        // else the tile with the smallest bound in the round with the smallest bound.  Which tile goes first never
+        // changes the result, only how many tiles are left.
+        int first = -1;
+        if (hint) {
+          const int h = mh[m];
+          if (h >= 0 && h < V) first = h >> 5;
         }
-        __syncwarp();
-        const float best0 = __uint_as_float((unsigned)(*reinterpret_cast<volatile unsigned long long*>(key + m) >> 32));
+        if (first < 0) {
+          const float rmin = redux_min_f32(rlb);
+          const unsigned bm = __ballot_sync(0xffffffffu, lane < nr && rlb == rmin);
+          const int r0 = bm ? __ffs(bm) - 1 : 0;
+          const float lb0 = nt_boxdist(box, ntp, r0 * 32 + lane, mx, my, mz);
+          const float tmin = redux_min_f32(lb0);
+          const unsigned bt = __ballot_sync(0xffffffffu, lb0 == tmin);
+          first = r0 * 32 + (bt ? __ffs(bt) - 1 : 0);
+        }
+        // lane-local lexicographic minimum of (distance, original id << 16 | row); inf / NaN never win (the
+        // exhaustive scan's strict '<' against an initial +inf never accepts them either)
+        float bd = INF;
+        unsigned bk = 0xffffffffu;
+        {
+          const int pos = min(first * 32 + lane, V - 1);
+          const float* p = raw + 3 * pos;
+          const float d = nt_sqdist(mx, my, mz, p[0], p[1], p[2]);
+          if (d < INF) { bd = d; bk = ((unsigned)ids_s[pos] << 16) | (unsigned)pos; }
+        }
+        const float best0 = redux_min_f32(bd);
         unsigned pend = __ballot_sync(0xffffffffu, lane < nr && !(rlb > best0));     // NaN bounds are never pruned
         while (pend) {
           const int r = __ffs(pend) - 1;
           pend &= pend - 1;
-          lb = nt_boxdist(box, ntp, r * 32 + lane, mx, my, mz);
-          const bool cand = !(lb > best0) && !(r == r0 && lane == j0) && r * 32 + lane != th;
-          const unsigned cb = __ballot_sync(0xffffffffu, cand);
-          if (!cb) continue;
-          const int n = __popc(cb);
-          unsigned base = 0;
-          if (lane == 0) base = atomicAdd(&list_count, (unsigned)n);
-          base = __shfl_sync(0xffffffffu, base, 0);
-          const unsigned slot = base + __popc(cb & ((1u << lane) - 1u));
-          const bool stored = cand && slot < NP_LIST;
-          __threadfence_block();                 // key[m] (initialised above) is visible before the pair that refers to it
-          if (stored) list[slot] = ((unsigned)m << 16) | (unsigned)(r * 32 + lane);
-          unsigned over = __ballot_sync(0xffffffffu, cand && !stored);           // list full: evaluate here
-          while (over) {
-            const int j = __ffs(over) - 1;
-            over &= over - 1;
-            np_eval_merge(raw, ids, V, r * 32 + j, lane, mx, my, mz, key + m);
-          }
-        }
-      }
-      // this warp has appended all its pairs (writes before the count: a consumer that sees nwarp here sees them all)
-      __syncwarp();
-      if (lane == 0) { __threadfence_block(); atomicAdd(&producers_done, 1u); }
-      NP_TICK(3);   // 3a (no barrier: a warp that is done producing starts draining right away)
-      // ---- 3b. drain the pair list: one lane per HALF pair (16 vertices walked serially, rotated start as in step 2:
-      // no bank conflicts whatever the tiles are), 16 pairs per warp-step handed out by an atomic cursor; the
-      // lane-local lexicographic minimum of (distance, original id) is merged with one atomicMin.  Pairs may still
-      // be arriving: a lane waits until its slot is reserved (or every producer is done) and then until it is written.
-      for (;;) {
-        unsigned qb = 0;
-        if (lane == 0) qb = atomicAdd(&list_next, 16u);
-        qb = __shfl_sync(0xffffffffu, qb, 0);
-        if (qb >= NP_LIST) break;
-        const unsigned q = qb + (lane & 15);
-        const int rot = lane & 15;
-        bool mine = false;
-        for (unsigned spins = 0;; ++spins) {
-          const bool done = *reinterpret_cast<volatile unsigned*>(&producers_done) == (unsigned)nwarp;
-          const unsigned cnt = min(*reinterpret_cast<volatile unsigned*>(&list_count), (unsigned)NP_LIST);
-          if (q < cnt) { mine = true; break; }
-          if (done) break;                       // cnt was read after done: it is final
-          if (spins > (1u << 26)) __trap();      // a protocol bug must not hang the box
-        }
-        if (!__any_sync(0xffffffffu, mine)) {    // nothing left in [qb, qb+16) and nothing more will come
-          if (*reinterpret_cast<volatile unsigned*>(&producers_done) == (unsigned)nwarp &&
-              qb >= min(*reinterpret_cast<volatile unsigned*>(&list_count), (unsigned)NP_LIST)) break;
-          continue;
-        }
-        if (mine) {
-          unsigned e = *reinterpret_cast<volatile unsigned*>(list + q);
-          for (unsigned spins = 0; e == 0xffffffffu; ++spins) {
-            e = *reinterpret_cast<volatile unsigned*>(list + q);
-            if (spins > (1u << 26)) __trap();
-          }
-          const int m = (int)(e >> 16), t = (int)(e & 0xffffu);
-          const float mx = mk[3 * m], my = mk[3 * m + 1], mz = mk[3 * m + 2];
-          const int p0 = t * 32 + (lane >> 4) * 16;
-          float dbest = INF;
-          int pbest = -1;
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int pos = min(p0 + ((i + rot) & 15), V - 1);
+          const float lb = nt_boxdist(box, ntp, r * 32 + lane, mx, my, mz);
+          unsigned cb = __ballot_sync(0xffffffffu, !(lb > best0) && r * 32 + lane != first);
+#ifdef NP_TIMING
+          if (blockIdx.x == 0 && lane == 0) atomicAdd(&np_phase_cycles[6], (unsigned long long)__popc(cb));
+#endif
+          while (cb) {
+            const int j = __ffs(cb) - 1;
+            cb &= cb - 1;
+            const int pos = min((r * 32 + j) * 32 + lane, V - 1);
             const float* p = raw + 3 * pos;
             const float d = nt_sqdist(mx, my, mz, p[0], p[1], p[2]);
-            if (d < dbest) { dbest = d; pbest = pos; }
-            else if (d == dbest && pbest >= 0 && pos != pbest) {          // exact tie inside the half tile: original ids decide
-              const int ia = ids ? __ldg(ids + pos) : pos, ib = ids ? __ldg(ids + pbest) : pbest;
-              if (ia < ib) pbest = pos;
-            }
-          }
-          if (pbest >= 0 && __float_as_uint(dbest) < 0x7f800000u) {        // inf / NaN never win
-            const int id = ids ? __ldg(ids + pbest) : pbest;
-            const unsigned long long k = np_pack(dbest, id, pbest);
-            if (k < *reinterpret_cast<volatile unsigned long long*>(key + m)) atomicMin(key + m, k);
+            const unsigned k = ((unsigned)ids_s[pos] << 16) | (unsigned)pos;
+            if (d < bd || (d == bd && k < bk && d < INF)) { bd = d; bk = k; }
           }
         }
+        const float dm = redux_min_f32(bd);
+        const unsigned kk = __reduce_min_sync(0xffffffffu, bd == dm ? bk : 0xffffffffu);
+        if (lane == 0) {
+          const bool none = kk == 0xffffffffu;             // no finite distance: (inf, 0) like the exhaustive scan
+          dist2[o] = none ? INF : dm;
+          idx[o] = none ? 0 : (int)(kk >> 16);
+          if (pos_out) pos_out[o] = none ? 0 : (int)(kk & 0xffffu);
+        }
       }
-      __syncthreads();
-      NP_TICK(4);   // 3b
-      // ---- 3c. results
-      for (int m = tid; m < mc; m += nthr) {
-        const unsigned long long k = key[m];
-        const unsigned id = (unsigned)(k >> 16) & 0xffffu, ps = (unsigned)k & 0xffffu;
-        const bool none = id == 0xffffu && ps == 0xffffu && (unsigned)(k >> 32) == 0x7f800000u;
-        dist2[(size_t)f * M + m0 + m] = __uint_as_float((unsigned)(k >> 32));
-        idx[(size_t)f * M + m0 + m] = none ? 0 : (int)id;        // all-NaN distances: (inf, 0) like the exhaustive scan
-        if (pos_out) pos_out[(size_t)f * M + m0 + m] = none ? 0 : (int)ps;
-      }
-      if (m0 + NP_MAXM < M) __syncthreads();
+      NP_TICK(3);   // markers (this warp's)
+      __syncthreads();                                     // every warp is done with the markers / this frame's buffers
+      NP_TICK(4);   // waiting for the other warps
     }
-    __syncthreads();                                     // every warp is done with this frame's buffer
-    NP_TICK(5);   // 3c
+    NP_TICK(5);
 #ifdef NP_TIMING
-    if (blockIdx.x == 0 && threadIdx.x == 0) { np_phase_cycles[6] += list_count; np_phase_cycles[7] += 1; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) np_phase_cycles[7] += 1;
 #endif
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
