@@ -152,3 +152,35 @@ def test_sub_hierarchies_match_reference_golden():
     for k, ref in g["subtrees"].items():
         assert sub_hierarchies(g["parents"], int(k)) == ref, k
     assert sub_hierarchies(g["parents"], 99) == [sorted(range(24))]
+
+
+def test_stageii_writer_roundtrip(tmp_path):
+    """test/test.py:115-143: keys, shapes, per-stage file names; axis-angle vs scipy (angle in [0, pi])."""
+    from scipy.spatial.transform import Rotation
+    from uuo_mocap_b200 import stageii
+    F = 7
+    rot = Rotation.random(F * 24, random_state=11)
+    R = torch.from_numpy(rot.as_matrix().astype(np.float32)).reshape(F, 24, 3, 3)
+    R[0, 0] = torch.eye(3)                                        # identity: the small-angle branch
+    R[1, 0] = torch.tensor([[-1.0, 0, 0], [0, -1.0, 0], [0, 0, 1.0]])   # a half turn
+    aa = stageii.matrix_to_axis_angle(R)
+    back = Rotation.from_rotvec(aa.reshape(-1, 3).numpy().astype(np.float64)).as_matrix().reshape(F, 24, 3, 3)
+    assert np.abs(back - R.numpy()).max() < 2e-6
+    assert float(aa.norm(dim=-1).max()) <= np.pi + 1e-5 and float(aa[0, 0].abs().max()) == 0.0
+    ref = rot.as_rotvec().reshape(F, 24, 3)
+    ok = np.ones((F, 24), bool)
+    ok[0, 0] = ok[1, 0] = False
+    assert np.abs(aa.numpy()[ok] - ref[ok]).max() < 2e-5
+    name = str(tmp_path / "take_stageii.npz")
+    mk = np.random.default_rng(0).normal(size=(F, 41, 3)).astype(np.float32)
+    stages = {"chamfer": {"trans": np.zeros((F, 3), np.float32), "betas": np.ones((1, 10), np.float32),
+                          "root_orient": R[:, :1].numpy(), "pose_body": R[:, 1:].numpy()}}
+    out = stageii.save_stageii(name, torch.arange(10.0).reshape(1, 10), torch.ones(F, 3), R[:, :1], R[:, 1:], 120, mk,
+                               stages=stages)
+    z = stageii.load_stageii(name)
+    assert sorted(z) == ["betas", "gender", "mocap_frame_rate", "mocap_markers", "poses", "trans"]
+    assert z["betas"].shape == (10,) and z["trans"].shape == (F, 3) and z["poses"].shape == (F, 72)
+    assert str(z["gender"]) == "neutral" and int(z["mocap_frame_rate"]) == 120 and np.array_equal(z["mocap_markers"], mk)
+    assert np.array_equal(z["poses"], out["poses"])
+    zs = stageii.load_stageii(str(tmp_path / "take_stageii.chamfer.npz"))
+    assert zs["betas"].shape == (1, 10) and np.array_equal(zs["poses"], z["poses"]) and float(zs["trans"].sum()) == 0.0

@@ -3,13 +3,17 @@ reference's stage functions (same names and argument meaning as
 /root/reference/src/video_mocap/optimization.py).
 
 A closure evaluation is a fixed sequence of C-ABI calls, no autograd graph and no [F,M,V] tensor:
-  chamfer stage (optimization.py:187-275):
-      uuo_lbs_forward(RAW6D, yaw) -> uuo_nn_argmin -> uuo_chamfer_rows -> uuo_lbs_backward_rows
-      -> uuo_sqdiff_accumulate (video-pose prior, betas prior) [-> uuo_transvel_accumulate]
+  chamfer stage (optimization.py:187-275), on the visiting-order twin model (``SMPL.visiting_twin``):
+      uuo_lbs_forward(RAW6D, yaw) -> uuo_nn_argmin_presorted_fit (marker mask as weights, the previous
+      iteration's matches as hint) -> uuo_chamfer_rows -> uuo_lbs_backward_rows_cached (v_posed rows taken
+      from the dense forward's workspace) -> uuo_sqdiff_accumulate (video-pose prior, betas prior)
+      [-> uuo_transvel_accumulate]
   marker stage (optimization.py:329-394):
-      uuo_lbs_forward_rows -> uuo_marker_loss_rows -> uuo_lbs_backward_rows -> priors [-> uuo_temporal_accumulate]
-followed by uuo_adam_step over the flat parameter block (north-star optimiser) or torch.optim.LBFGS
-(the reference's optimiser) driving the same closure.
+      uuo_lbs_forward_rows -> uuo_marker_loss_rows -> uuo_lbs_backward_rows_cached -> priors
+      [-> uuo_temporal_accumulate]
+followed by uuo_adam_step(_dev) over the flat parameter block (north-star optimiser; with one process and no
+per-iteration callback the whole iteration is replayed from a CUDA graph) or torch.optim.LBFGS (the
+reference's optimiser) driving the same closure.
 
 Frame-range sharding (``Shard``): every rank owns a contiguous frame range; per iteration the ranks
 all-reduce ONE 16-float buffer (d/d betas + loss) and, only when a temporal term is enabled, exchange
