@@ -300,6 +300,7 @@ extern "C" int uuo_debug_nn_phases(unsigned long long* out, int reset) {
 #endif
 
 #define NP_THREADS 1024
+#define NP_GROUP 512         // threads per half-CTA
 #define NP_MAXM 256          // markers per pass over a frame
 
 struct np_layout {
@@ -313,8 +314,8 @@ __host__ __device__ inline np_layout np_make_layout(int V) {
   L.ntp = L.nr * 32;
   L.stage_floats = (3 * V + 8 + 3) & ~3;
   L.off_box = (size_t)2 * L.stage_floats * 4;
-  L.off_rbox = L.off_box + (size_t)6 * L.ntp * 4;
-  L.off_mk = L.off_rbox + 6 * 32 * 4;                 // two buffers each: this frame's and the next frame's
+  L.off_rbox = L.off_box + (size_t)2 * 6 * L.ntp * 4;  // boxes, round boxes, markers: one set per half-CTA
+  L.off_mk = L.off_rbox + 2 * 6 * 32 * 4;
   L.off_mw = L.off_mk + 2 * NP_MAXM * 3 * 4;
   L.off_mh = L.off_mw + 2 * NP_MAXM * 4;
   L.off_ids = L.off_mh + 2 * NP_MAXM * 4;
@@ -331,22 +332,26 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
                                                                      int32_t* __restrict__ idx,
                                                                      int32_t* pos_out) {   // may alias hint
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = NP_THREADS, nwarp = NP_THREADS / 32;
+  // two half-CTAs of 16 warps work on ALTERNATE frames (group g owns staging buffer g, box set g, marker buffers g and
+  // named barrier 1 + g): one group's boxes, barrier tails and load wait overlap the other group's markers
+  const int tid = threadIdx.x, lane = tid & 31, g = tid >> 9, gt = tid & (NP_GROUP - 1), warp = gt >> 5, nthr = NP_GROUP,
+            nwarp = NP_GROUP / 32;
+  auto gbar = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "n"(NP_GROUP) : "memory"); };
   const np_layout L = np_make_layout(V);
   const int nr = L.nr, ntp = L.ntp, nflt = 3 * V;
   float* stage0 = reinterpret_cast<float*>(smem_raw);
-  float* box = reinterpret_cast<float*>(smem_raw + L.off_box);
-  float* rbox = reinterpret_cast<float*>(smem_raw + L.off_rbox);
+  float* box = reinterpret_cast<float*>(smem_raw + L.off_box) + (size_t)g * 6 * L.ntp;
+  float* rbox = reinterpret_cast<float*>(smem_raw + L.off_rbox) + g * 6 * 32;
   float* mk0 = reinterpret_cast<float*>(smem_raw + L.off_mk);
   float* mw0 = reinterpret_cast<float*>(smem_raw + L.off_mw);      // marker weights: a marker of weight 0 is not searched
   int* mh0 = reinterpret_cast<int*>(smem_raw + L.off_mh);          // hinted row per marker
   unsigned short* ids_s = reinterpret_cast<unsigned short*>(smem_raw + L.off_ids);   // original id of every row
-  for (int i = tid; i < ntp * 32; i += nthr) {
+  for (int i = tid; i < ntp * 32; i += NP_THREADS) {
     const int p = min(i, V - 1);
     ids_s[i] = (unsigned short)(ids ? __ldg(ids + p) : p);
   }
   __shared__ __align__(8) uint64_t load_bar[2];
-  __shared__ unsigned marker_next;     // markers handed out to warps so far
+  __shared__ unsigned marker_next[2];  // markers handed out to the group's warps so far
   const float INF = __int_as_float(0x7f800000);
   if (tid == 0) {
     umma::mbar_init(umma::smem_u32(&load_bar[0]), 1);
@@ -362,18 +367,18 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
   // stage frame f into buffer b (see nn_tiles_kernel: bulk copy of the 16 B hull, cp.async for out-of-tensor hulls)
   // and, with cp.async, the first NP_MAXM markers of that frame with their weights and hints
   auto issue_load = [&](int f, int b) {
-    if (tid >= NP_THREADS / 2) {             // the upper warps build no boxes
-      const int t = tid - NP_THREADS / 2, mc = min(NP_MAXM, M);
-      for (int i = t; i < mc * 3; i += NP_THREADS / 2) cp_async4(mk0 + b * NP_MAXM * 3 + i, markers + (size_t)f * M * 3 + i);
+    {
+      const int mc = min(NP_MAXM, M);
+      for (int i = gt; i < mc * 3; i += nthr) cp_async4(mk0 + b * NP_MAXM * 3 + i, markers + (size_t)f * M * 3 + i);
       if (wts)
-        for (int i = t; i < mc; i += NP_THREADS / 2) cp_async4(mw0 + b * NP_MAXM + i, wts + (size_t)f * M + i);
+        for (int i = gt; i < mc; i += nthr) cp_async4(mw0 + b * NP_MAXM + i, wts + (size_t)f * M + i);
       if (hint)
-        for (int i = t; i < mc; i += NP_THREADS / 2) cp_async4(mh0 + b * NP_MAXM + i, hint + (size_t)f * M + i);
+        for (int i = gt; i < mc; i += nthr) cp_async4(mh0 + b * NP_MAXM + i, hint + (size_t)f * M + i);
     }
     const float* src = vertices + (size_t)f * nflt;
     float* stage = stage0 + (size_t)b * L.stage_floats;
     if (hull_ok(f)) {
-      if (tid == NP_THREADS - 32) {
+      if (gt == NP_GROUP - 32) {
         const uint32_t bar = umma::smem_u32(&load_bar[b]);
         const uintptr_t a = reinterpret_cast<uintptr_t>(src), lo = a & ~(uintptr_t)15;
         const uint32_t bytes = (uint32_t)(((a + (size_t)nflt * 4 + 15) & ~(uintptr_t)15) - lo);
@@ -389,27 +394,25 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
       const int head = min(nflt, (4 - mis) & 3);
       const int body = (nflt - head) >> 2;
       const int tail0 = head + 4 * body;
-      if (tid < head) cp_async4(raw + tid, src + tid);
-      for (int i = tid; i < body; i += nthr) cp_async16(raw + head + 4 * i, src + head + 4 * i);
-      if (tid < nflt - tail0) cp_async4(raw + tail0 + tid, src + tail0 + tid);
+      if (gt < head) cp_async4(raw + gt, src + gt);
+      for (int i = gt; i < body; i += nthr) cp_async16(raw + head + 4 * i, src + head + 4 * i);
+      if (gt < nflt - tail0) cp_async4(raw + tail0 + gt, src + tail0 + gt);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  uint32_t parity[2] = {0, 0};
-  if ((int)blockIdx.x < F) issue_load(blockIdx.x, 0);
+  uint32_t parity = 0;
+  const int fstep = 2 * (int)gridDim.x, f0 = (int)blockIdx.x + g * (int)gridDim.x, buf = g;
+  if (f0 < F) issue_load(f0, buf);
 
-  int buf = 0;
 #ifdef NP_TIMING
   long long tick_ = clock64();
 #endif
-  for (int f = blockIdx.x; f < F; f += gridDim.x, buf ^= 1) {
+  for (int f = f0; f < F; f += fstep) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-    if (hull_ok(f)) { umma::mbar_wait(umma::smem_u32(&load_bar[buf]), parity[buf]); parity[buf] ^= 1; }
-    __syncthreads();
+    if (hull_ok(f)) { umma::mbar_wait(umma::smem_u32(&load_bar[buf]), parity); parity ^= 1; }
+    gbar();
     NP_TICK(0);   // wait for the frame
-    // the other buffers were last read during the previous frame, which ended with a barrier: stream the next frame in
-    if (f + (int)gridDim.x < F) issue_load(f + gridDim.x, buf ^ 1);
-    if (tid == 0) marker_next = 0;
+    if (gt == 0) marker_next[g] = 0;
     const float* raw = stage0 + (size_t)buf * L.stage_floats +
                        (int)((reinterpret_cast<uintptr_t>(vertices + (size_t)f * nflt) & 15) >> 2);
     float* mk = mk0 + buf * NP_MAXM * 3;
@@ -438,7 +441,7 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
         box[3 * ntp + t] = hx; box[4 * ntp + t] = hy; box[5 * ntp + t] = hz;
       }
     }
-    __syncthreads();
+    gbar();
     NP_TICK(1);   // tile boxes
     for (int r = warp; r < nr; r += nwarp) {
       const int t = r * 32 + lane;
@@ -453,19 +456,19 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
     for (int m0 = 0; m0 < M; m0 += NP_MAXM) {
       const int mc = min(NP_MAXM, M - m0);
       if (m0 > 0) {                                        // later chunks of a large marker set: fetched in place
-        for (int i = tid; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
-        for (int i = tid; i < mc; i += nthr) {
+        for (int i = gt; i < mc * 3; i += nthr) mk[i] = __ldg(markers + ((size_t)f * M + m0) * 3 + i);
+        for (int i = gt; i < mc; i += nthr) {
           if (wts) mw[i] = __ldg(wts + (size_t)f * M + m0 + i);
           if (hint) mh[i] = hint[(size_t)f * M + m0 + i];   // a plain load: pos_out may be the same buffer
         }
-        if (tid == 0) marker_next = 0;
+        if (gt == 0) marker_next[g] = 0;
       }
-      __syncthreads();                                     // round boxes, markers, counter
+      gbar();                                              // round boxes, markers, counter
       NP_TICK(2);
       // ---- 3. markers, handed out one by one (their costs differ a lot)
       for (;;) {
         int m = 0;
-        if (lane == 0) m = (int)atomicAdd(&marker_next, 1u);
+        if (lane == 0) m = (int)atomicAdd(&marker_next[g], 1u);
         m = __shfl_sync(0xffffffffu, m, 0);
         if (m >= mc) break;
         const size_t o = (size_t)f * M + m0 + m;
@@ -537,9 +540,11 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
         }
       }
       NP_TICK(3);   // markers (this warp's)
-      __syncthreads();                                     // every warp is done with the markers / this frame's buffers
+      gbar();                                              // every warp is done with the markers / this frame's buffers
       NP_TICK(4);   // waiting for the other warps
     }
+    // the group's buffers are free: stream its next frame in (the other group computes meanwhile)
+    if (f + fstep < F) issue_load(f + fstep, buf);
     NP_TICK(5);
 #ifdef NP_TIMING
     if (blockIdx.x == 0 && threadIdx.x == 0) np_phase_cycles[7] += 1;
