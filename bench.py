@@ -377,9 +377,14 @@ def run_fit(args, rank, world, local, dev):
         roofline = dict(r_ch or {})
         roofline.setdefault("traffic", None)
         roofline["marker_stage"] = r_mk
-        cpu = None
+        cpu = tg = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = cpu_closure_rate(args.ref_frames, cap, model)
+            try:                              # a reported bar, never a reason to lose the bench line
+                torch.cuda.empty_cache()
+                tg = cpu_closure_rate(min(F, 2048), cap, model, device=dev)
+            except Exception as e:
+                tg = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:160])}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": 2 * K, "warmup": args.warmup,
             "ms_per_step": (ms_ch + ms_mk) / (2 * K), "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
@@ -394,32 +399,38 @@ def run_fit(args, rank, world, local, dev):
                     "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d Adam iterations "
                             "per stage, one H2D of the capture and one D2H of the fitted parameters per call" % K},
             "gpu_launches": int(sum(v[1] for v in (prof_ch or {}).values()) + sum(v[1] for v in (prof_mk or {}).values())),
-            "roofline": roofline, "cpu_baseline": cpu,
+            "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
         }
         _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
-def cpu_closure_rate(frames, cap, model):
-    """Oracle chamfer + marker closures (fwd + bwd) + torch Adam on the host cores, `frames` frames."""
+def cpu_closure_rate(frames, cap, model, device=None):
+    """Oracle chamfer + marker closures (fwd + bwd) + torch Adam on the host cores, `frames` frames.
+    With ``device``: the same torch ops on that CUDA device through stock PyTorch kernels (the SURVEY.md 8(d)
+    "composition" bar of the fitting loop), timed with a synchronize on both sides of every iteration."""
     from oracle import closures
     from oracle.smpl_oracle import OracleSMPL
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     orc = OracleSMPL.from_model(model)
+    on_gpu = device is not None
+    if on_gpu:
+        orc = orc.to(device)
+    sync = (lambda: torch.cuda.synchronize(device)) if on_gpu else (lambda: None)
     sl = slice(0, frames)
-    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[sl]))
-    mk, opose, obetas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas)
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[sl])).to(device if on_gpu else "cpu")
+    mk, opose, obetas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas).to(device if on_gpu else "cpu")
     root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
-    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, mk.shape[1]).astype(np.int64))
+    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, mk.shape[1]).astype(np.int64)).to(mk.device)
     res = {}
     for stage in ("chamfer", "marker"):
         pose = opose.clone().requires_grad_(True)
         betas = obetas.clone().requires_grad_(True)
         tr = trans.clone().requires_grad_(True)
         if stage == "chamfer":
-            z = torch.zeros(frames, 1, 1, requires_grad=True)
+            z = torch.zeros(frames, 1, 1, device=mk.device, requires_grad=True)
             params = [tr, z, betas, pose]
             fn = lambda: closures.chamfer_stage_loss(orc, mk, pose, opose, betas, obetas, root, tr, z,
                                                      {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0})
@@ -431,12 +442,18 @@ def cpu_closure_rate(frames, cap, model):
         opt = torch.optim.Adam(params, lr=0.01)
         ts = []
         for i in range(3):
+            sync()
             t0 = time.perf_counter()
             opt.zero_grad()
             fn().backward()
             opt.step()
+            sync()
             ts.append(time.perf_counter() - t0)
         res[stage + "_s"] = float(np.median(ts[1:]))
+    if on_gpu:
+        return {"value": 2 * frames / (res["chamfer_s"] + res["marker_s"]), "unit": UNIT, "frames": frames,
+                "kind": "oracle chamfer + marker closures (fwd+bwd) + torch Adam through stock PyTorch CUDA ops (fp32, TF32 off), "
+                        "frame chunks of 256, median of 2 after 1 warm-up", "chamfer_s": res["chamfer_s"], "marker_s": res["marker_s"]}
     return {"value": 2 * frames / (res["chamfer_s"] + res["marker_s"]), "unit": UNIT, "cores": threads, "kind": "port",
             "sample": "%d frames, chamfer + marker closure (fwd+bwd) + Adam, median of 2 after 1 warm-up, torch threads=%d"
                       % (frames, threads),

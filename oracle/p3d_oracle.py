@@ -125,7 +125,7 @@ def axis_angle_to_matrix(axis_angle: torch.Tensor) -> torch.Tensor:
 
 def compute_root_orient_z(angle: torch.Tensor) -> torch.Tensor:
     """src/video_mocap/optimization.py:672-679 -- [...,1] yaw angle -> [...,3,3]."""
-    z = torch.zeros(list(angle.shape[:-1]) + [3])
+    z = torch.zeros(list(angle.shape[:-1]) + [3], dtype=angle.dtype, device=angle.device)
     z[..., [2]] = angle
     return axis_angle_to_matrix(z)
 
@@ -147,8 +147,8 @@ class _KnnK1(torch.autograd.Function):
     @staticmethod
     def forward(ctx, p1, p2, chunk):
         N, P1, _ = p1.shape
-        dists = torch.empty(N, P1, dtype=p1.dtype)
-        idx = torch.empty(N, P1, dtype=torch.long)
+        dists = torch.empty(N, P1, dtype=p1.dtype, device=p1.device)
+        idx = torch.empty(N, P1, dtype=torch.long, device=p1.device)
         for s in range(0, N, chunk):
             e = min(N, s + chunk)
             d = sqdist_matrix(p1[s:e], p2[s:e])
