@@ -473,6 +473,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-frames", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-sync", action="store_true", help="lbs e2e: one synchronous call per step instead of the double-buffered loop")
     ap.add_argument("--no-graph", action="store_true", help="fit workloads: time eager launches instead of graph replays")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -560,23 +561,78 @@ def main():
     h2d = sum(x.numel() * 4 for x in (h_go, h_bp, h_betas, h_tr))
     d2h = h2d + 4
 
-    def step_e2e():
-        d = [x.to(dev, non_blocking=True).requires_grad_(True) for x in (h_go, h_bp, h_betas, h_tr)]
-        o = smpl(betas=d[2], body_pose=d[1], global_orient=d[0], transl=d[3], pose2rot=False)
-        # the upstream gradients g_vertices / g_joints are inputs of the workload:
-        # they go straight into autograd, no [F,V,3] elementwise "loss" kernels of torch's in the timed region
-        torch.autograd.backward([o.vertices, o.joints], [gv, gj])
-        for dst, src in zip(h_out, d):
-            dst.copy_(src.grad, non_blocking=True)
-        h_loss.copy_((o.joints.detach() * gj).sum().reshape(1), non_blocking=True)   # the step's scalar result
-        torch.cuda.current_stream().synchronize()   # the caller reads it
+    hosts = (h_go, h_bp, h_betas, h_tr)
+    if args.e2e_sync:
+        def step_e2e(i):
+            d = [x.to(dev, non_blocking=True).requires_grad_(True) for x in hosts]
+            o = smpl(betas=d[2], body_pose=d[1], global_orient=d[0], transl=d[3], pose2rot=False)
+            # the upstream gradients g_vertices / g_joints are inputs of the workload:
+            # they go straight into autograd, no [F,V,3] elementwise "loss" kernels of torch's in the timed region
+            torch.autograd.backward([o.vertices, o.joints], [gv, gj])
+            for dst, src in zip(h_out, d):
+                dst.copy_(src.grad, non_blocking=True)
+            h_loss.copy_((o.joints.detach() * gj).sum().reshape(1), non_blocking=True)   # the step's scalar result
+            torch.cuda.current_stream().synchronize()   # the caller reads it
 
+        def drain():
+            pass
+    else:
+        # the loop a caller with a stream of host batches writes: the copies of step i+1 (in) and step i-1 (out) run on a
+        # copy stream under the kernels of step i; every step still copies its own inputs in and its own results out
+        cs = torch.cuda.Stream(device=dev)
+        d_in = [[torch.empty(x.shape, device=dev).requires_grad_(True) for x in hosts] for _ in range(2)]
+        h_outs = [[torch.empty_like(x).pin_memory() for x in hosts] for _ in range(2)]
+        h_losses = [torch.empty(1).pin_memory() for _ in range(2)]
+        ev = lambda: [torch.cuda.Event(), torch.cuda.Event()]
+        in_ready, comp_done, out_done = ev(), ev(), ev()
+        keep = [None, None]
+
+        def issue_h2d(slot):
+            with torch.cuda.stream(cs), torch.no_grad():
+                for dst, src in zip(d_in[slot], hosts):
+                    dst.copy_(src, non_blocking=True)
+                in_ready[slot].record(cs)
+
+        def step_e2e(i):
+            slot = i & 1
+            cur = torch.cuda.current_stream()
+            cur.wait_event(in_ready[slot])
+            issue_h2d(slot ^ 1)                       # next step's inputs (its buffers were released by out_done below)
+            d = d_in[slot]
+            for t_ in d:
+                t_.grad = None
+            o = smpl(betas=d[2], body_pose=d[1], global_orient=d[0], transl=d[3], pose2rot=False)
+            torch.autograd.backward([o.vertices, o.joints], [gv, gj])
+            loss = (o.joints.detach() * gj).sum().reshape(1)
+            comp_done[slot].record(cur)
+            keep[slot] = [t_.grad for t_ in d] + [loss]
+            with torch.cuda.stream(cs):
+                cs.wait_event(comp_done[slot])
+                for dst, g_ in zip(h_outs[slot], keep[slot][:4]):
+                    dst.copy_(g_, non_blocking=True)
+                h_losses[slot].copy_(loss, non_blocking=True)
+                out_done[slot].record(cs)
+            if i > 0:
+                out_done[slot ^ 1].synchronize()      # the caller reads the PREVIOUS step's gradients and scalar
+
+        def drain():
+            torch.cuda.current_stream().wait_stream(cs)
+
+        issue_h2d(0)
+
+    n_e2e = 0
     for _ in range(args.warmup):
-        step_e2e()
+        step_e2e(n_e2e)
+        n_e2e += 1
+    drain()
     barrier()
+    if not args.e2e_sync:
+        issue_h2d(n_e2e & 1)                          # inside the timed region: K steps = K copies in, K copies out
     e0.record()
     for _ in range(args.steps):
-        step_e2e()
+        step_e2e(n_e2e)
+        n_e2e += 1
+    drain()
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
@@ -639,7 +695,9 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD % F, "frames_per_gpu": F, "parallelism": "frame-range shards x%d" % world,
                        "l2": "inputs larger than L2 (>= 680 MB streamed per step)"},
-            "clocks": clocks, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "clocks": clocks, "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                                      "mode": "one synchronous call per step" if args.e2e_sync else
+                                      "double-buffered: copies of step i+1 (in) / i-1 (out) on a copy stream under the kernels of step i"},
             "gpu_launches": launches_per_step * args.steps, "roofline": roofline,
             "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
         }
