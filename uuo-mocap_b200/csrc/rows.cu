@@ -234,7 +234,7 @@ __global__ void cache_vposed_rows_kernel(const float* __restrict__ vposed, int N
 }
 
 template <bool CACHED>
-__global__ void __launch_bounds__(ROWS_WARPS * 32) rows_backward_kernel(
+__global__ void __launch_bounds__(ROWS_WARPS * 32, 9) rows_backward_kernel(
     const float* __restrict__ vt, const float* __restrict__ Bt, const float* __restrict__ W, int KP, int J,
     const float* __restrict__ coef, const float* __restrict__ A, int F, const int32_t* __restrict__ rows,
     int rows_shared, int R, const float* __restrict__ g_rows, const float* __restrict__ rowbuf,
@@ -249,14 +249,14 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32) rows_backward_kernel(
   const float4* s_coef4 = reinterpret_cast<const float4*>(s_coef_all[w]);
   const float4* s_A4 = reinterpret_cast<const float4*>(s_A_all[w]);
   RowRec* rec = s_rec_all[w];
-  float gc[ROWS_MAXKP / 32];   // d coef, k = lane + 32 q
-#pragma unroll
-  for (int q = 0; q < ROWS_MAXKP / 32; ++q) gc[q] = 0.f;
+  // d coef: lane owns k = 4 lane .. 4 lane + 3 and 128 + 4 lane .. (KP <= 256): two 16 B loads per Bt row
+  float4 gc0 = make_float4(0.f, 0.f, 0.f, 0.f), gc1 = gc0;
+  const bool has1 = 128 + 4 * lane < KP;
+  const int kp4 = KP >> 2;
   float ga[12];                // d A[j = lane][ab]
 #pragma unroll
   for (int i = 0; i < 12; ++i) ga[i] = 0.f;
   float gs = 0.f;              // lane a < 3: sum of g over rows (d transl)
-  const int nq = KP >> 5;
 
   for (int c0 = 0; c0 < R; c0 += ROWS_CHUNK) {
     const int nc = min(ROWS_CHUNK, R - c0);
@@ -295,14 +295,21 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32) rows_backward_kernel(
       if (v < 0) continue;                                              // warp-uniform
       const float4 q1 = reinterpret_cast<const float4*>(rec + r)[1];   // gvp
       const float4 q2 = reinterpret_cast<const float4*>(rec + r)[2];   // g
-      const float* b = Bt + (size_t)(3 * v) * KP + lane;
-#pragma unroll
-      for (int q = 0; q < ROWS_MAXKP / 32; ++q)
-        if (q < nq) {
-          gc[q] = fmaf(q1.x, __ldg(b + 32 * q), gc[q]);
-          gc[q] = fmaf(q1.y, __ldg(b + KP + 32 * q), gc[q]);
-          gc[q] = fmaf(q1.z, __ldg(b + 2 * KP + 32 * q), gc[q]);
-        }
+      const float4* b4 = reinterpret_cast<const float4*>(Bt + (size_t)(3 * v) * KP) + lane;
+      {
+        const float4 x = __ldg(b4), y = __ldg(b4 + kp4), z = __ldg(b4 + 2 * kp4);
+        gc0.x = fmaf(q1.z, z.x, fmaf(q1.y, y.x, fmaf(q1.x, x.x, gc0.x)));
+        gc0.y = fmaf(q1.z, z.y, fmaf(q1.y, y.y, fmaf(q1.x, x.y, gc0.y)));
+        gc0.z = fmaf(q1.z, z.z, fmaf(q1.y, y.z, fmaf(q1.x, x.z, gc0.z)));
+        gc0.w = fmaf(q1.z, z.w, fmaf(q1.y, y.w, fmaf(q1.x, x.w, gc0.w)));
+      }
+      if (has1) {
+        const float4 x = __ldg(b4 + 32), y = __ldg(b4 + kp4 + 32), z = __ldg(b4 + 2 * kp4 + 32);
+        gc1.x = fmaf(q1.z, z.x, fmaf(q1.y, y.x, fmaf(q1.x, x.x, gc1.x)));
+        gc1.y = fmaf(q1.z, z.y, fmaf(q1.y, y.y, fmaf(q1.x, x.y, gc1.y)));
+        gc1.z = fmaf(q1.z, z.z, fmaf(q1.y, y.z, fmaf(q1.x, x.z, gc1.z)));
+        gc1.w = fmaf(q1.z, z.w, fmaf(q1.y, y.w, fmaf(q1.x, x.w, gc1.w)));
+      }
       if (lane < 3) gs += lane == 0 ? q2.x : (lane == 1 ? q2.y : q2.z);
       // dA[j][a][b] += W[v][j] g[a] vh[b],  vh = (v_posed, 1)
       const float wj = lane < J ? __ldg(W + (size_t)v * J + lane) : 0.f;
@@ -326,10 +333,9 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32) rows_backward_kernel(
     d4[2] = make_float4(ga[8], ga[9], ga[10], ga[11]);
   }
   if (lane < 4) dstA[J * 12 + lane] = (lane < 3) ? gs : 0.f;
-  float* dstC = gcoef_part + (size_t)f * KP;
-#pragma unroll
-  for (int q = 0; q < ROWS_MAXKP / 32; ++q)
-    if (q < nq) dstC[lane + 32 * q] = gc[q];
+  float4* dstC = reinterpret_cast<float4*>(gcoef_part + (size_t)f * KP);
+  if (4 * lane < KP) dstC[lane] = gc0;
+  if (has1) dstC[32 + lane] = gc1;
 }
 
 static int rows_check(const uuo_model* m) {
