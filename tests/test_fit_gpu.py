@@ -281,3 +281,18 @@ def test_adam_graph_replay_equals_eager(ctx):
         ops.adam_step_dev(s2[0], g, s2[1], s2[2], 0.01, cnt)
     assert int(cnt.item()) == 5
     assert torch.allclose(s1[0], s2[0], rtol=1e-6, atol=1e-7)
+
+
+def test_marker_labels_from_coords_and_weighted_mse(ctx):
+    """optimization.py:645-659, :718-724."""
+    from uuo_mocap_b200.fit import compute_marker_labels_from_coords, weighted_mse_loss
+    model, smpl, _ = ctx
+    vids = torch.tensor([5, 900, 3000, 6889, 5])
+    one_hot = torch.zeros(5, 6890)
+    one_hot[torch.arange(5), vids] = 1.0
+    want = torch.from_numpy(np.argmax(model.weights, axis=-1))[vids]
+    for arg in (one_hot, vids):
+        lab = compute_marker_labels_from_coords(smpl, arg, 7)
+        assert lab.shape == (7, 5) and torch.equal(lab.cpu(), want.unsqueeze(0).expand(7, 5))
+    a, b, w = torch.randn(4, 3, device="cuda:0"), torch.randn(4, 3, device="cuda:0"), torch.rand(4, 3, device="cuda:0")
+    assert torch.allclose(weighted_mse_loss(a, b, w), (((a - b) ** 2) * w).mean())

@@ -338,6 +338,21 @@ def get_marker_mask(markers: torch.Tensor) -> torch.Tensor:
     return ops.get_marker_mask(markers) != 0
 
 
+def compute_marker_labels_from_coords(smpl_inference, barycentric_coords_one_hot: torch.Tensor, num_frames: int) -> torch.Tensor:
+    """optimization.py:645-659: body-part label [F,M] of every marker = the joint with the largest skinning weight at
+    the marker's vertex.  ``barycentric_coords_one_hot``: the [M,V] one-hot matrix or the vertex-index vector [M]."""
+    smpl = _model_of(smpl_inference)
+    vertex_ids = torch.argmax(smpl.lbs_weights, dim=-1)
+    c = barycentric_coords_one_hot.to(smpl.device)
+    coords_ids = torch.argmax(c, dim=-1) if c.dim() == 2 else c.long()
+    return vertex_ids[coords_ids].unsqueeze(0).repeat_interleave(int(num_frames), dim=0)
+
+
+def weighted_mse_loss(input: torch.Tensor, target: torch.Tensor, weights: torch.Tensor) -> torch.Tensor:
+    """optimization.py:718-724."""
+    return torch.mean(torch.nn.functional.mse_loss(input, target, reduction="none") * weights)
+
+
 def weighted_chamfer_distance(x: torch.Tensor, y: torch.Tensor, x_weights: torch.Tensor,
                               single_directional: bool = False, return_idx: bool = False, model=None):
     """src/video_mocap/losses/chamfer_distance.py:5-21 (always single-directional there): value only, no
