@@ -154,7 +154,7 @@ def test_nn_argmin_presorted_bit_exact(F, M, V, ties, with_ids):
     assert torch.equal(d.cpu(), d_ref)
 
 
-@pytest.mark.parametrize("F,M,V", [(5, 45, 6890), (3, 300, 515), (150, 45, 6890)])
+@pytest.mark.parametrize("F,M,V", [(5, 45, 6890), (3, 300, 515), (150, 45, 6890), (2, 7, 19), (4, 1, 1), (301, 3, 33)])
 @pytest.mark.parametrize("hint_kind", [None, "good", "garbage"])
 def test_nn_argmin_presorted_fit_weights_and_hints(F, M, V, hint_kind):
     """uuo_nn_argmin_presorted_fit: weight-0 markers report (0, ids[0], 0), every other marker is bit-exact whatever
@@ -166,6 +166,8 @@ def test_nn_argmin_presorted_fit_weights_and_hints(F, M, V, hint_kind):
     rng = np.random.default_rng(F * 7 + M)
     w = torch.from_numpy((rng.uniform(size=(F, M)) > 0.3).astype(np.float32) * rng.uniform(0.5, 2.0, size=(F, M)).astype(np.float32))
     w[0] = 0.0                                         # a frame with every marker dropped
+    if F > 1 and float(w[1:].sum()) == 0.0:
+        w[1] = 1.0
     m[w == 0] = 0.0                                    # dropped markers sit at the origin like the reference's
     perm = rng.permutation(V)
     ids = torch.from_numpy(perm.astype(np.int32)).cuda()
@@ -229,3 +231,16 @@ def test_visiting_twin_matches_model(get_model):
     flat[1:] = b.vertices.detach().reshape(-1)
     d2, i2 = ops.nn_argmin_presorted(mk, flat[1:].view_as(b.vertices), twin.visit_ids)
     assert torch.equal(d0, d2) and torch.equal(i0, i2)
+
+
+def test_nn_argmin_presorted_fit_empty_inputs():
+    from uuo_mocap_b200 import ops
+    m = torch.zeros(0, 5, 3, device="cuda:0")
+    v = torch.zeros(0, 64, 3, device="cuda:0")
+    d, i, p = ops.nn_argmin_presorted(m, v, None, want_pos=True, weights=torch.zeros(0, 5, device="cuda:0"),
+                                      hint=torch.zeros(0, 5, dtype=torch.int32, device="cuda:0"))
+    assert d.shape == (0, 5) and i.shape == (0, 5) and p.shape == (0, 5)
+    m = torch.zeros(3, 0, 3, device="cuda:0")
+    v = torch.randn(3, 64, 3, device="cuda:0")
+    d, i = ops.nn_argmin_presorted(m, v, None, hint=torch.zeros(3, 0, dtype=torch.int32, device="cuda:0"))
+    assert d.shape == (3, 0)

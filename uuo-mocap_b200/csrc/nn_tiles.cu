@@ -556,12 +556,12 @@ __global__ void __launch_bounds__(NP_THREADS, 1) nn_presorted_kernel(const float
 static int nn_presorted_launch(const float* markers, const float* vertices, const int32_t* ids, const float* weights,
                                const int32_t* hint, int F, int M, int V, float* dist2, int32_t* idx, int32_t* pos,
                                void* stream) {
-  UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
   UUO_CHECK_ARG(F >= 0 && M >= 0 && V > 0, "bad sizes");
   const np_layout L = np_make_layout(V);
   UUO_CHECK_ARG(V < 65535 && L.nr <= 32 && L.total <= 227 * 1024 && M < 65536,
                 "V too large for the presorted correspondence kernel (two staged frames must fit in shared memory)");
-  if (F == 0 || M == 0) return UUO_OK;
+  if (F == 0 || M == 0) return UUO_OK;                     // empty inputs: nothing to read, pointers may be NULL
+  UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
   static thread_local size_t configured = 0;
   static thread_local int n_sm = 0;
   if (L.total > configured) {
