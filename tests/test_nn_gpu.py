@@ -244,3 +244,15 @@ def test_nn_argmin_presorted_fit_empty_inputs():
     v = torch.randn(3, 64, 3, device="cuda:0")
     d, i = ops.nn_argmin_presorted(m, v, None, hint=torch.zeros(3, 0, dtype=torch.int32, device="cuda:0"))
     assert d.shape == (3, 0)
+
+
+def test_nn_argmin_empty_inputs_all_kernels(get_model):
+    """F == 0 or M == 0 through the exhaustive, the box-pruned and the presorted entry points: empty outputs, no error."""
+    from uuo_mocap_b200 import ops
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    smpl = SMPL(_as_struct(get_model("top4")), device="cuda:0")
+    for F, M in ((0, 5), (3, 0)):
+        m = torch.zeros(F, M, 3, device="cuda:0")
+        v = torch.randn(F, 6890, 3, device="cuda:0")
+        for d, i in (ops.nn_argmin(m, v), ops.nn_argmin(m, v, model=smpl.handle), ops.nn_argmin_presorted(m, v, None)):
+            assert d.shape == (F, M) and i.shape == (F, M)

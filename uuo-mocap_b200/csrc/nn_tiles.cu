@@ -232,8 +232,9 @@ __global__ void __launch_bounds__(1024, 1) nn_tiles_kernel(const float* __restri
 
 extern "C" int uuo_nn_argmin_ordered(const float* markers, const float* vertices, const int32_t* order, int F, int M,
                                      int V, float* dist2, int32_t* idx, void* stream) {
-  UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
   UUO_CHECK_ARG(F >= 0 && M >= 0 && V > 0, "bad sizes");
+  if (F == 0 || M == 0) return UUO_OK;                     // empty inputs: nothing to read, pointers may be NULL
+  UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
   const nt_layout L = nt_make_layout(V);
   const size_t smem = L.total;
   if (!order || V > 65535 || L.nr > 32 || smem > 227 * 1024)      // no order / does not fit: the exhaustive kernel
