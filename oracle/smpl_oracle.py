@@ -1,6 +1,6 @@
 """Oracle restatement of the smplx SMPL layer (TEST INFRASTRUCTURE, CPU, fp32).
 
-PINNED against the reference's own code: ``tests/test_oracle_vs_smplx.py`` runs the vendored
+PINNED against the reference's own code: ``tests/test_oracle_smplx.py`` runs the vendored
 ``/root/reference/third_party/smplx`` on the same inputs (when that tree is present) and
 requires bit-identical vertices/joints/gradients, and ``tests/golden/smplx_*.npz`` holds
 outputs produced by that real reference (``oracle/gen_golden.py``).
