@@ -703,6 +703,8 @@ def main():
                                       "double-buffered: copies of step i+1 (in) / i-1 (out) on a copy stream under the kernels of step i"},
             "gpu_launches": launches_per_step * args.steps, "roofline": roofline,
             "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
+            "note": "value: direct C-ABI calls with the library's per-kernel CUDA events ON over the timed region (they "
+                    "feed roofline.ms_per_launch; ~1-2 % overhead); e2e: SMPL.forward + autograd, events off",
         }
         _emit(line)
     if world > 1:
