@@ -221,14 +221,15 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
     prob.red.zero_()
     brows = prob.betas_rows(v["betas"])
     with torch.cuda.device(prob.dev):
-        virt = prob.lbs_forward_rows(brows, v["root_orient"], v["pose_body"], None, v["trans"], vertex_idx, True)
+        shared = vertex_idx.dim() == 1          # [M]: one vertex per marker for every frame; [F,M]: per frame (stacked hypotheses)
+        virt = prob.lbs_forward_rows(brows, v["root_orient"], v["pose_body"], None, v["trans"], vertex_idx, shared)
         if "marker" in losses:                                                          # :356-362 (mean over ALL F*M)
             check(_lib.lib().uuo_marker_loss_rows(ptr(prob.markers), ptr(virt), ptr(prob.mask), F * M, MARKER_DISTANCE,
                                                   losses["marker"] / (Fg * M), ptr(prob.red[15:]), ptr(prob.g_rows),
                                                   prob._st()))
         else:
             prob.g_rows.zero_()
-        prob.lbs_backward_rows(brows, v["root_orient"], v["pose_body"], None, vertex_idx, True, prob.g_rows,
+        prob.lbs_backward_rows(brows, v["root_orient"], v["pose_body"], None, vertex_idx, shared, prob.g_rows,
                                prob.gbetas_target(), g["root_orient"], g["pose_body"], None, g["trans"], cached=True)
         if "reg_pose_body" in losses:                                                   # :363-365
             prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
@@ -421,8 +422,10 @@ def optim_markers(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
     prob = problem or FitProblem(smpl_inference, markers, o_pose_body, o_betas, shard, groups)
     dev = prob.dev
     vidx = barycentric_coords_one_hot
-    if vidx.dim() == 2:
+    if vidx.dim() == 2 and vidx.is_floating_point():      # the reference's [M,V] one-hot matrix
         vidx = torch.argmax(vidx, dim=1)
+    elif vidx.dim() == 2 and vidx.shape != (prob.F, prob.M):
+        raise ValueError("per-frame vertex indices must be [F, M]")
     vidx = vidx.to(dev, torch.int32).contiguous()
     pb = ParamBlock.build({"pose_body": pose_body, "betas": betas.reshape(-1, prob.mh.NB), "root_orient": root_orient,
                            "trans": trans}, dev)
@@ -504,13 +507,14 @@ def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient,
         sl = slice(h * F, (h + 1) * F)
         vidx.append(compute_nearest_points(mk[sl], pose[sl], bet[h:h + 1], root[sl], tr[sl], smpl, img_mask=img_mask,
                                            config=config, shard=shard, as_one_hot=False))
+    # marker stage of all hypotheses as ONE stacked problem: every frame carries its hypothesis' vertex indices
+    vall = torch.cat([v.to(dev, torch.int32).reshape(1, -1).expand(F, -1) for v in vidx], dim=0).contiguous()
+    optim_markers(mk, pose, opose, bet, obet, root, tr, vall, None, smpl, config, shard=shard, groups=H, problem=prob)
     scores, fitted = [], []
     for h in range(H):
         sl = slice(h * F, (h + 1) * F)
         p = {"pose_body": pose[sl].clone(), "betas": bet[h:h + 1].clone(), "root_orient": root[sl].clone(),
              "trans": tr[sl].clone()}
-        optim_markers(mk[sl], p["pose_body"], opose[sl], p["betas"], obet, p["root_orient"], p["trans"], vidx[h],
-                      img_mask, smpl, config, shard=shard)
         out = smpl(betas=p["betas"], body_pose=normalize_rot(p["pose_body"]), global_orient=normalize_rot(p["root_orient"]),
                    transl=p["trans"], pose2rot=False)
         val, _ = weighted_chamfer_distance(mk[sl], out.vertices, ops.get_marker_mask(mk[sl]))
