@@ -244,6 +244,8 @@ def run_fit(args, rank, world, local, dev):
         loss_ch["trans_vel"] = 1.0
         loss_mk["temporal"] = 1.0
     vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, M).astype(np.int32)).to(dev)
+    if groups > 1:  # every hypothesis carries its own correspondences (fit.fit_hypotheses): indices [groups, M]
+        vidx = vidx.reshape(1, M).expand(groups, M).contiguous()
     state = {k: (torch.zeros_like(pb.flat), torch.zeros_like(pb.flat)) for k, pb in (("ch", pb_ch), ("mk", pb_mk))}
     counters = {k: torch.zeros(1, dtype=torch.int32, device=dev) for k in ("ch", "mk")}
     graphs = {}

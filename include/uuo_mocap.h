@@ -82,8 +82,10 @@ int uuo_lbs_backward(const uuo_model* m, const float* betas, int betas_rows, con
                      float* g_transl, void* stream);
 
 /* Backward for a gradient that touches only R vertex rows per frame (what the chamfer and marker
- * losses produce): rows[F,R] vertex ids (or rows[R] when rows_shared), g_rows[F,R,3].  Same outputs
- * as uuo_lbs_backward; never touches a dense [F,V,3] gradient. */
+ * losses produce): g_rows[F,R,3].  Same outputs as uuo_lbs_backward; never touches a dense [F,V,3] gradient.
+ * rows_shared selects the layout of rows (here and in the other *_rows entry points):
+ *   0: rows[F,R], one set per frame;  1: rows[R], the same set for every frame;
+ *   G > 1: rows[G,R], frame f uses set f / (F/G) (G hypotheses stacked along the frame axis, F % G == 0). */
 int uuo_lbs_backward_rows(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
                           const float* body_pose, int pose_mode, const float* yaw, int F,
                           const int32_t* rows, int rows_shared, int R, const float* g_rows,

@@ -180,7 +180,8 @@ def test_stacked_hypotheses_equal_separate_fits(ctx):
 
 
 @pytest.mark.parametrize("kind", ["top4", "dense"])
-@pytest.mark.parametrize("shared,R,F", [(True, 45, 130), (True, 7, 3), (False, 45, 70), (False, 64, 5), (True, 80, 9)])
+@pytest.mark.parametrize("shared,R,F", [(1, 45, 130), (1, 7, 3), (0, 45, 70), (0, 64, 5), (1, 80, 9),
+                                        (2, 45, 140), (3, 7, 9), (4, 41, 512)])   # > 1: that many row groups
 def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
     """uuo_lbs_forward_rows == gather of the dense forward; uuo_lbs_backward_rows (re-evaluating v_posed) ==
     uuo_lbs_backward_rows_cached (v_posed from the forward / from uuo_lbs_cache_vposed_rows) == the dense backward
@@ -197,9 +198,12 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
     rot = torch.from_numpy(mb["rot"] + 0.05 * rng.normal(size=mb["rot"].shape).astype(np.float32)).to(dev)
     go, bp = rot[:, :1].contiguous(), rot[:, 1:].contiguous()
     betas, transl = torch.from_numpy(mb["betas"][:1]).to(dev), torch.from_numpy(mb["transl"]).to(dev)
-    if shared:
+    if shared == 1:
         rows = torch.from_numpy(rng.choice(V, size=R, replace=False).astype(np.int32)).to(dev)
         rows_f = rows.long().unsqueeze(0).expand(F, R)
+    elif shared > 1:      # rows[G,R]: frame f uses set f // (F // G)
+        rows = torch.from_numpy(rng.integers(0, V, size=(shared, R)).astype(np.int32)).to(dev)
+        rows_f = rows.long().repeat_interleave(F // shared, dim=0)
     else:
         rows = torch.from_numpy(rng.integers(0, V, size=(F, R)).astype(np.int32)).to(dev)
         rows_f = rows.long()
@@ -222,7 +226,7 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
     outs["dense"] = gd
     out_rows = torch.empty((F, R, 3), device=dev)
     check(L.uuo_lbs_forward_rows(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, ptr(transl), F, ptr(rows),
-                                 1 if shared else 0, R, ptr(out_rows), None, ptr(ws), st))
+                                 int(shared), R, ptr(out_rows), None, ptr(ws), st))
     ref_rows = torch.gather(verts, 1, rows_f.unsqueeze(-1).expand(F, R, 3))
     assert rel_err(out_rows.cpu().numpy(), ref_rows.cpu().numpy()) < 1e-5
     variants = [("recompute", L.uuo_lbs_backward_rows)]
@@ -230,7 +234,7 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
         variants.append(("cached", L.uuo_lbs_backward_rows_cached))
     for name, fn in variants:
         g = grads()
-        check(fn(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(rows), 1 if shared else 0, R,
+        check(fn(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(rows), int(shared), R,
                  ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]), ptr(g[2]), None, ptr(g[3]), st))
         outs[name] = g
     if R <= 64:   # v_posed rows picked out of a dense forward's workspace by position (= vertex id on the model itself)
@@ -240,7 +244,7 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
         check(L.uuo_lbs_cache_vposed_rows(mh.handle, F, ptr(pos), R, ptr(ws), st))
         g = grads()
         check(L.uuo_lbs_backward_rows_cached(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F, ptr(rows),
-                                             1 if shared else 0, R, ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]),
+                                             int(shared), R, ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]),
                                              ptr(g[2]), None, ptr(g[3]), st))
         outs["cached_from_dense"] = g
     for name, g in outs.items():

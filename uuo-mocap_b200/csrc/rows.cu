@@ -7,12 +7,22 @@
 // transform blend, the 3x4 apply) runs ONE ROW PER LANE -- no cross-lane reductions; the frame's coefficients
 // and transforms are staged in shared memory and read as broadcasts.  Only the two reductions OVER rows of the
 // backward (d coef, d A) run row by row with lanes across the coefficient / joint axis.
+#include <algorithm>
+
 #include "common.cuh"
 
 #define FULL 0xffffffffu
 #define ROWS_WARPS 4
 #define ROWS_MAXKP 256      // KP <= 256
 #define ROWS_CHUNK 64       // rows staged per pass of the backward
+
+// rows[] layout: rows_shared == 0: [F][R] (per frame); == 1: [R] (all frames); == G > 1: [G][R], frame f belongs to
+// group f / (F / G) (stacked hypotheses: every block of F / G frames has its own correspondences)
+__device__ __forceinline__ size_t rows_base(int rows_shared, int F, int f, int R) {
+  if (rows_shared == 0) return (size_t)f * R;
+  if (rows_shared == 1) return 0;
+  return (size_t)(f / (F / rows_shared)) * R;
+}
 
 struct __align__(16) RowRec {
   float vp[3];
@@ -94,7 +104,7 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32) rows_forward_kernel(
   for (int r0 = 0; r0 < R; r0 += 32) {
     const int r = r0 + lane;
     if (r >= R) break;
-    const int v = rows_shared ? rows[r] : rows[(size_t)f * R + r];
+    const int v = rows[rows_base(rows_shared, F, f, R) + r];
     float vp[3], T[12];
     lane_vposed(vt, Bt, KP, s_coef4, v, vp);
     if (rowbuf) reinterpret_cast<float4*>(rowbuf)[(size_t)f * ROWS_CHUNK + r] = make_float4(vp[0], vp[1], vp[2], 0.f);
@@ -145,6 +155,15 @@ __global__ void __launch_bounds__(ROWSS_WARPS * 32, 1) rows_forward_shared_kerne
   float* s_A = reinterpret_cast<float*>(smem_raw + L.off_A) + w * ROWSS_NF * UUO_SKIN_J * 12;      // [NF][J][12]
   float* s_vp = reinterpret_cast<float*>(smem_raw + L.off_vp) + w * ROWSS_NF * 32 * ROWSS_NI;      // [NF][3R]
   const int n3 = L.n3, pitch = L.pitch;
+  if (gridDim.y > 1) {       // grouped rows: group g = blockIdx.y owns frames [g F, (g+1) F) and rows[g][R]
+    const size_t fb = (size_t)blockIdx.y * F;
+    rows += (size_t)blockIdx.y * R;
+    coef += fb * KP;
+    A += fb * J * 12;
+    if (transl) transl += fb * 3;
+    out_rows += fb * R * 3;
+    if (rowbuf) rowbuf += fb * ROWS_CHUNK * 4;
+  }
   for (int i = tid; i < n3 * KP; i += ROWSS_WARPS * 32) {
     const int n = i / KP, k = i - n * KP;
     s_B[n * pitch + k] = __ldg(Bt + (size_t)(3 * rows[n / 3] + n % 3) * KP + k);
@@ -264,7 +283,7 @@ __global__ void __launch_bounds__(ROWS_WARPS * 32, 9) rows_backward_kernel(
     for (int r0 = 0; r0 < nc; r0 += 32) {
       const int r = r0 + lane;
       if (r < nc) {
-        const int v = rows_shared ? rows[c0 + r] : rows[(size_t)f * R + c0 + r];
+        const int v = rows[rows_base(rows_shared, F, f, R) + c0 + r];
         const float* gp = g_rows + ((size_t)f * R + c0 + r) * 3;
         const float g0 = gp[0], g1 = gp[1], g2 = gp[2];
         RowRec o;
@@ -351,7 +370,9 @@ int launch_rows_forward(const uuo_model* m, const float* transl, int F, const in
   float* rowbuf = R <= ROWS_CHUNK ? ws.rowbuf : nullptr;
   const rowss_layout L = rowss_make_layout(m->KP, R, m->J);
   ProfScope ps_("rows_forward", st);
-  if (rows_shared && 3 * R <= 32 * ROWSS_NI && L.total <= 227 * 1024 && F >= 64) {
+  const int G = rows_shared > 1 ? rows_shared : 1;           // rows_shared = G > 1: G contiguous frame groups, rows[G][R]
+  if (F % G) { uuo_set_error("rows path: F must be a multiple of the number of row groups"); return UUO_ERR_ARG; }
+  if (rows_shared && 3 * R <= 32 * ROWSS_NI && L.total <= 227 * 1024 && F / G >= 64) {
     static thread_local size_t configured = 0;
     static thread_local int n_sm = 0;
     if (L.total > configured) {
@@ -363,9 +384,11 @@ int launch_rows_forward(const uuo_model* m, const float* transl, int F, const in
       UUO_CUDA(cudaGetDevice(&dev));
       UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     }
-    const int need = (F + ROWSS_WARPS * ROWSS_NF - 1) / (ROWSS_WARPS * ROWSS_NF);
-    rows_forward_shared_kernel<<<need < n_sm ? need : n_sm, ROWSS_WARPS * 32, L.total, st>>>(
-        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows, R, out_rows, rowbuf);
+    const int Fg = F / G;
+    const int need = (Fg + ROWSS_WARPS * ROWSS_NF - 1) / (ROWSS_WARPS * ROWSS_NF);
+    const int per_group = std::max(1, std::min(need, (n_sm + G - 1) / G));
+    rows_forward_shared_kernel<<<dim3(per_group, G), ROWSS_WARPS * 32, L.total, st>>>(
+        m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, Fg, rows, R, out_rows, rowbuf);
   } else {
     rows_forward_kernel<<<(F + ROWS_WARPS - 1) / ROWS_WARPS, ROWS_WARPS * 32, 0, st>>>(
         m->vt, m->Bt, m->W, m->KP, m->J, ws.coef, ws.A, transl, F, rows, rows_shared, R, out_rows, rowbuf);

@@ -92,7 +92,7 @@ class FitProblem:
     def lbs_forward_rows(self, betas_rows, root, pose, yaw, trans, rows, shared):
         R = rows.shape[-1]
         check(_lib.lib().uuo_lbs_forward_rows(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
-                                              POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(rows), 1 if shared else 0, R,
+                                              POSE_RAW6D, ptr(yaw), ptr(trans), self.F, ptr(rows), int(shared), R,
                                               ptr(self.virt), None, ptr(self.ws), self._st()))
         return self.virt
 
@@ -108,7 +108,7 @@ class FitProblem:
                                                            self._st()))
             fn = _lib.lib().uuo_lbs_backward_rows_cached
         check(fn(self.mh.handle, ptr(betas_rows), betas_rows.shape[0], ptr(root), ptr(pose),
-                                               POSE_RAW6D, ptr(yaw), self.F, ptr(rows), 1 if shared else 0, R,
+                                               POSE_RAW6D, ptr(yaw), self.F, ptr(rows), int(shared), R,
                                                ptr(g_rows), None, ptr(self.ws), ptr(g_betas), ptr(g_root), ptr(g_pose),
                                                ptr(g_yaw), ptr(g_trans), self._st()))
 
@@ -221,7 +221,13 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
     prob.red.zero_()
     brows = prob.betas_rows(v["betas"])
     with torch.cuda.device(prob.dev):
-        shared = vertex_idx.dim() == 1          # [M]: one vertex per marker for every frame; [F,M]: per frame (stacked hypotheses)
+        # rows mode of the C-ABI: 1 = [M] for every frame; G = [G,M], one set per stacked hypothesis; 0 = [F,M] per frame
+        if vertex_idx.dim() == 1:
+            shared = 1
+        elif prob.groups > 1 and vertex_idx.shape[0] == prob.groups and prob.groups != F:
+            shared = prob.groups
+        else:
+            shared = 0
         virt = prob.lbs_forward_rows(brows, v["root_orient"], v["pose_body"], None, v["trans"], vertex_idx, shared)
         if "marker" in losses:                                                          # :356-362 (mean over ALL F*M)
             check(_lib.lib().uuo_marker_loss_rows(ptr(prob.markers), ptr(virt), ptr(prob.mask), F * M, MARKER_DISTANCE,
@@ -424,8 +430,8 @@ def optim_markers(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
     vidx = barycentric_coords_one_hot
     if vidx.dim() == 2 and vidx.is_floating_point():      # the reference's [M,V] one-hot matrix
         vidx = torch.argmax(vidx, dim=1)
-    elif vidx.dim() == 2 and vidx.shape != (prob.F, prob.M):
-        raise ValueError("per-frame vertex indices must be [F, M]")
+    elif vidx.dim() == 2 and tuple(vidx.shape) not in ((prob.F, prob.M), (prob.groups, prob.M)):
+        raise ValueError("vertex indices must be [M], [groups, M] or [F, M]")
     vidx = vidx.to(dev, torch.int32).contiguous()
     pb = ParamBlock.build({"pose_body": pose_body, "betas": betas.reshape(-1, prob.mh.NB), "root_orient": root_orient,
                            "trans": trans}, dev)
@@ -507,8 +513,10 @@ def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient,
         sl = slice(h * F, (h + 1) * F)
         vidx.append(compute_nearest_points(mk[sl], pose[sl], bet[h:h + 1], root[sl], tr[sl], smpl, img_mask=img_mask,
                                            config=config, shard=shard, as_one_hot=False))
-    # marker stage of all hypotheses as ONE stacked problem: every frame carries its hypothesis' vertex indices
-    vall = torch.cat([v.to(dev, torch.int32).reshape(1, -1).expand(F, -1) for v in vidx], dim=0).contiguous()
+    # marker stage of all hypotheses as ONE stacked problem: one set of vertex indices per hypothesis [H,M]
+    vall = torch.stack([v.to(dev, torch.int32).reshape(-1) for v in vidx], dim=0).contiguous()
+    if H == 1:
+        vall = vall[0]
     optim_markers(mk, pose, opose, bet, obet, root, tr, vall, None, smpl, config, shard=shard, groups=H, problem=prob)
     scores, fitted = [], []
     for h in range(H):
