@@ -5,8 +5,8 @@ reference's stage functions (same names and argument meaning as
 A closure evaluation is a fixed sequence of C-ABI calls, no autograd graph and no [F,M,V] tensor:
   chamfer stage (optimization.py:187-275), on the visiting-order twin model (``SMPL.visiting_twin``):
       uuo_lbs_forward(RAW6D, yaw) -> uuo_nn_argmin_presorted_fit (marker mask as weights, the previous
-      iteration's matches as hint) -> uuo_chamfer_rows -> uuo_lbs_backward_rows_cached (v_posed rows taken
-      from the dense forward's workspace) -> uuo_sqdiff_accumulate (video-pose prior, betas prior)
+      iteration's matches as hint) -> uuo_chamfer_rows -> uuo_lbs_cache_vposed_rows -> uuo_lbs_backward_rows_cached
+      (v_posed rows taken from the dense forward's workspace) -> uuo_sqdiff_accumulate (video-pose prior, betas prior)
       [-> uuo_transvel_accumulate]
   marker stage (optimization.py:329-394):
       uuo_lbs_forward_rows -> uuo_marker_loss_rows -> uuo_lbs_backward_rows_cached -> priors
