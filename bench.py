@@ -530,7 +530,9 @@ def main():
                                 ptr(joints), ptr(ws), st))
         check(L.uuo_lbs_backward(mh.handle, ptr(betas), F, ptr(go), ptr(bp), 0, None, F, ptr(gv), ptr(gj), ptr(ws),
                                  ptr(g_betas), ptr(g_go), ptr(g_bp), None, ptr(g_tr), st))
-    launches_per_step = 10   # fk, transform pack, gemm, skin, extra-joint gather | skin-bwd x2, gemm^T, fk-bwd, beta-grad copy
+    # per step (profiles/r1i_ncu_summary.txt): fk_forward, pack_transforms, vposed gemm, skin fwd, extra_joints |
+    # skin bwd (d v_posed), extras_vposed, skin bwd (d A), extras_dA, gcoef gemm, fk_backward, copy_gbetas
+    launches_per_step = 12
 
     def barrier():
         if world > 1:
