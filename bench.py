@@ -176,7 +176,7 @@ def run_reference(args, rank, world):
 FIT_TRAFFIC_KEYS = ("nn_argmin_presorted", "rows_forward", "rows_backward", "adam_step")
 FIT_WORKLOADS = {
     # name: (description, total frames, hypotheses, scaling, temporal terms)
-    "fit5k": ("configs[2]: video_mocap.yaml fit, 5000 frames per GPU, 41 markers + 4 ghosts, noise 2 mm, dropout 5 %%, "
+    "fit5k": ("configs[2]: video_mocap.yaml fit, 5000 frames per GPU, 41 markers + 4 ghosts, noise 2 mm, dropout 5 %, "
               "synthetic video-pose prior", 5000, 1, "weak", False),
     "mht": ("configs[3]: mht_rotation.yaml, 64 yaw hypotheses x 2000 frames stacked along the frame axis and sharded by "
             "hypothesis", 2000, 64, "strong", False),
