@@ -184,3 +184,38 @@ def test_stageii_writer_roundtrip(tmp_path):
     assert np.array_equal(z["poses"], out["poses"])
     zs = stageii.load_stageii(str(tmp_path / "take_stageii.chamfer.npz"))
     assert zs["betas"].shape == (1, 10) and np.array_equal(zs["poses"], z["poses"]) and float(zs["trans"].sum()) == 0.0
+
+
+@pytest.mark.parametrize("img_freq,mocap_freq", [(30.0, 120.0), (30.0, 100.0), (60.0, 50.0), (30.0, 30.0)])
+def test_resample_prior_matches_reference_loop(img_freq, mocap_freq):
+    """multimodal.py:144-182 restated frame by frame, rotations through scipy's Slerp (shortest great arc, what
+    roma.utils.unitquat_slerp traces whatever the component order): frame count, the repeated tail, linear terms."""
+    from scipy.spatial.transform import Rotation, Slerp
+    from uuo_mocap_b200 import stageii
+    F, J = 9, 24
+    rng = np.random.default_rng(5)
+    rot = Rotation.random(F * J, random_state=3).as_matrix().reshape(F, J, 3, 3)
+    rot[3] = rot[2]                                               # identical neighbours: the small-angle branch
+    R = torch.from_numpy(rot.astype(np.float32))
+    trans = torch.from_numpy(rng.normal(size=(F, 3)).astype(np.float32))
+    foot = torch.from_numpy(rng.random(size=(F, 2)).astype(np.float32))
+    t, ro, pb, fc = stageii.resample_prior(trans, R[:, :1], R[:, 1:], foot, img_freq, mocap_freq)
+    if img_freq == mocap_freq:
+        assert t is trans and fc is foot and ro.shape[0] == F
+        return
+    n_new = round(F * (mocap_freq / img_freq))
+    assert t.shape == (n_new, 3) and ro.shape == (n_new, 1, 3, 3) and pb.shape == (n_new, J - 1, 3, 3) and fc.shape == (n_new, 2)
+    got = torch.cat((ro, pb), dim=1).numpy()
+    for i in range(n_new):
+        frame = int(i * (img_freq / mocap_freq))
+        alpha = i * (img_freq / mocap_freq) - frame
+        if frame + 1 < F:
+            assert np.abs(t[i].numpy() - (trans[frame + 1].numpy() * alpha + trans[frame].numpy() * (1 - alpha))).max() < 1e-6
+            assert np.abs(fc[i].numpy() - (foot[frame + 1].numpy() * alpha + foot[frame].numpy() * (1 - alpha))).max() < 1e-6
+            for j in range(J):
+                key = Rotation.from_matrix(np.stack((rot[frame, j], rot[frame + 1, j])))
+                ref = Slerp([0.0, 1.0], key)([alpha]).as_matrix()[0]
+                assert np.abs(got[i, j] - ref).max() < 5e-6, (i, j)
+        else:
+            assert torch.equal(t[i], trans[frame]) and torch.equal(fc[i], foot[frame])
+            assert np.array_equal(got[i], rot[frame].astype(np.float32))

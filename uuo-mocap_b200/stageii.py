@@ -6,8 +6,8 @@ Keys (AMASS / MoSh++ stage-II layout): ``betas [10]``, ``trans [F,3]``, ``poses 
 ``<name>_stageii.<stage>.npz`` with that stage's ``trans`` / ``betas`` / ``poses``.
 
 Host-side format code: tensors may live on the GPU, they are converted on their device and copied out once.
-Not built (N2, reader half): the PHALP/HMR ``.pkl`` prior with slerp resampling and the ``.c3d`` marker reader
-(``roma`` / ``ezc3d`` are not installable here).
+Input side (N2, reader half): ``resample_prior`` brings the video prior to the marker frame rate
+(multimodal.py:144-182).  Not built: the PHALP/HMR ``.pkl`` and ``.c3d`` file parsers (``ezc3d`` is not installable here).
 """
 from __future__ import annotations
 
@@ -48,6 +48,66 @@ def matrix_to_axis_angle(m: torch.Tensor) -> torch.Tensor:
     small = angles.abs() < 1e-6
     s = torch.where(small, 0.5 - angles * angles / 48.0, torch.sin(0.5 * angles) / torch.where(small, torch.ones_like(angles), angles))
     return q[..., 1:] / s
+
+
+def quaternion_to_matrix(q: torch.Tensor) -> torch.Tensor:
+    """(w, x, y, z) [...,4] -> [...,3,3] (pytorch3d.transforms.quaternion_to_matrix: scaled by 2 / |q|^2)."""
+    r, i, j, k = torch.unbind(q, -1)
+    two_s = 2.0 / (q * q).sum(-1)
+    o = torch.stack((1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+                     two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+                     two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
+    return o.reshape(q.shape[:-1] + (3, 3))
+
+
+def unitquat_slerp(q0: torch.Tensor, q1: torch.Tensor, alpha: torch.Tensor) -> torch.Tensor:
+    """Shortest-arc slerp of unit quaternions [...,4], ``alpha`` broadcastable to [...,1].
+
+    The reference calls ``roma.utils.unitquat_slerp`` (q0 * exp(alpha * log(q0^-1 q1)), multimodal.py:168-169) on
+    pytorch3d's WXYZ quaternions although roma reads XYZW.  The curve is the constant-speed great arc of S^3 from q0
+    to q1 (flipped when <q0, q1> < 0), which depends on the 4-vectors only and not on the component order, so the
+    closed form below gives the same rotations (``roma`` is not installable here: checked against scipy's Slerp)."""
+    d = (q0 * q1).sum(-1, keepdim=True)
+    q1 = torch.where(d < 0, -q1, q1)
+    omega = torch.acos(d.abs().clamp(max=1.0))
+    so = torch.sin(omega)
+    small = so < 1e-6
+    den = torch.where(small, torch.ones_like(so), so)
+    w0 = torch.where(small, 1.0 - alpha, torch.sin((1.0 - alpha) * omega) / den)
+    w1 = torch.where(small, alpha + torch.zeros_like(so), torch.sin(alpha * omega) / den)
+    q = w0 * q0 + w1 * q1
+    return q / q.norm(dim=-1, keepdim=True)
+
+
+def resample_prior(trans: torch.Tensor, root_orient: torch.Tensor, pose_body: torch.Tensor,
+                   foot_contacts: torch.Tensor, img_freq: float, mocap_freq: float):
+    """Video prior at ``img_freq`` -> the marker rate ``mocap_freq`` (multimodal.py:144-182): output frame i reads
+    source frame int(i * img_freq / mocap_freq) and the next one, translations and foot contacts blended linearly,
+    rotations ([F,1,3,3], [F,J-1,3,3]) by quaternion slerp; past the last source frame the frame is repeated.
+    Returns (trans, root_orient, pose_body, foot_contacts) with round(F * mocap_freq / img_freq) frames; the
+    inputs are returned untouched when the rates agree (:145)."""
+    if mocap_freq == img_freq:
+        return trans, root_orient, pose_body, foot_contacts
+    n_src = trans.shape[0]
+    n_new = round(n_src * (mocap_freq / img_freq))
+    pos = [i * (img_freq / mocap_freq) for i in range(n_new)]                   # python doubles, like :152-153
+    frame = [int(p) for p in pos]
+    dev = trans.device
+    f0 = torch.tensor(frame, dtype=torch.long, device=dev)
+    inside = f0 + 1 < n_src
+    f1 = torch.where(inside, f0 + 1, f0)
+    alpha = torch.tensor([p - f for p, f in zip(pos, frame)], dtype=torch.float32, device=dev)
+    alpha = torch.where(inside, alpha, torch.zeros_like(alpha))
+
+    def lerp(x):
+        a = alpha.reshape((-1,) + (1,) * (x.dim() - 1)).to(x.dtype)
+        return torch.where(inside.reshape(a.shape), x[f1] * a + x[f0] * (1.0 - a), x[f0])
+
+    def slerp(r):
+        q = unitquat_slerp(matrix_to_quaternion(r[f0]), matrix_to_quaternion(r[f1]), alpha.reshape(-1, 1, 1))
+        return torch.where(inside.reshape(-1, 1, 1, 1), quaternion_to_matrix(q).to(r.dtype), r[f0])
+
+    return lerp(trans), slerp(root_orient), slerp(pose_body), lerp(foot_contacts)
 
 
 def _np(x):
