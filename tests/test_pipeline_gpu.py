@@ -55,3 +55,21 @@ def test_fit_capture_end_to_end(get_model, tmp_path, with_root):
     assert z["poses"].shape == (F, 72) and z["betas"].shape == (10,)
     zs = stageii.load_stageii(str(tmp_path / "take_stageii.marker_final.npz"))
     assert zs["poses"].shape == (F, 72)
+
+
+def test_fit_capture_resamples_half_rate_prior(get_model):
+    """multimodal.py:144-182: a 50 Hz video prior under a 100 Hz capture is brought to the marker rate first."""
+    from uuo_mocap_b200 import fit, pipeline, synthetic
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    model = get_model("top4")
+    smpl = SMPL(_as_struct(model), device="cuda:0")
+    F = 24
+    cap = synthetic.make_capture(model, F, num_markers=41, seed=52, noise_std=0.001, permute=False)
+    cfg = fit.default_config(num_iters=20, optimizer="adam", lr=0.01)
+    mk = _T(cap.markers)
+    half = (_T(cap.prior_pose_body)[::2], _T(cap.prior_betas), _T(cap.prior_root_orient)[::2], _T(cap.prior_trans)[::2])
+    out = pipeline.fit_capture(mk, *half, smpl, cfg, mocap_frame_rate=100.0, img_frame_rate=50.0)
+    assert out["trans"].shape == (F, 3) and out["pose_body"].shape == (F, 23, 3, 3)
+    assert torch.isfinite(out["trans"]).all() and torch.isfinite(out["pose_body"]).all()
+    o2 = pipeline.fit_capture(mk, *half, smpl, cfg, mocap_frame_rate=100.0)       # no rate given: truncated (:191-199)
+    assert o2["trans"].shape == (F // 2, 3)

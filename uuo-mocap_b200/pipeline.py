@@ -16,17 +16,24 @@ import torch
 
 from . import fit
 from .root import optim_root
+from .stageii import resample_prior
 
 
 def fit_capture(markers: torch.Tensor, pose_body: torch.Tensor, betas: torch.Tensor, root_orient: torch.Tensor,
                 trans: torch.Tensor, smpl_inference, config: Dict, img_mask: Optional[torch.Tensor] = None,
                 marker_labels: Optional[torch.Tensor] = None, mocap_frame_rate: float = 120.0,
-                save_stages: bool = True, verbose: bool = False) -> Dict:
+                save_stages: bool = True, verbose: bool = False, img_frame_rate: Optional[float] = None) -> Dict:
     """markers [F,M,3]; the video prior: pose_body [F,23,3,3], betas [1,10], root_orient [F,1,3,3], trans [F,3] (the
     ``o_*`` tensors of multimodal.py:172-186).  Returns the dict of multimodal.py:680-706 (``betas`` repeated per frame,
-    rotations normalised, ``stages`` with numpy snapshots) plus ``scores`` / ``best_angle`` of the hypothesis loop."""
+    rotations normalised, ``stages`` with numpy snapshots) plus ``scores`` / ``best_angle`` of the hypothesis loop.
+    ``img_frame_rate``: rate of the video prior when it differs from ``mocap_frame_rate``; the prior is then resampled
+    to the marker rate first (multimodal.py:144-182)."""
     smpl = fit._model_of(smpl_inference)
     dev = smpl.device
+    if img_frame_rate is not None and img_frame_rate != mocap_frame_rate:
+        trans, root_orient, pose_body, _ = resample_prior(torch.as_tensor(trans), torch.as_tensor(root_orient),
+                                                          torch.as_tensor(pose_body), torch.as_tensor(trans),
+                                                          img_frame_rate, mocap_frame_rate)
     T = lambda t: torch.as_tensor(t).detach().to(dev, torch.float32).contiguous()
     mk = torch.nan_to_num(T(markers), nan=0.0)                                          # :188
     F = min(mk.shape[0], trans.shape[0])                                                # :191-199
