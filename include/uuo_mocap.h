@@ -191,6 +191,30 @@ int uuo_marker_mean(const float* markers, int F, int M, float* mm, void* stream)
 int uuo_transvel_accumulate(const float* trans, const float* mm, const float* prev, const float* next, int F,
                             float scale, float* loss_sum, float* g_trans, void* stream);
 
+/* ---- frame-range shards over peer-mapped device memory (NVLink P2P; csrc/peer.cu) ----
+ * Replaces nothing in the reference (it is single-device): this is the exchange step the
+ * sharded closures need -- the sum over shards of [d/d betas | loss] (betas are shared by all frames,
+ * src/video_mocap/optimization.py:165-174,255-258) and the 1-/2-frame halo of the temporal terms (:246-250,368-374) --
+ * done by kernels that write into the neighbour's mailbox, so an iteration holds no host-issued collective and can be
+ * captured in a CUDA graph on every rank.  One uuo_comm per rank; all ranks issue the same sequence of calls.
+ *   uuo_comm_create          allocates this rank's mailbox on `device` (library-owned memory)
+ *   uuo_comm_export          host buffer of uuo_comm_handle_bytes() bytes <- the mailbox's CUDA IPC handle
+ *   uuo_comm_connect         handles_host[world][handle_bytes] of all ranks (other processes; own entry ignored)
+ *   uuo_comm_connect_local   peers[world] created in THIS process (tests, or one process driving several GPUs)
+ *   uuo_comm_all_reduce_sum  x[n] (n <= 1024) <- sum over ranks, added in rank order on every rank
+ *   uuo_comm_halo_exchange   x[F,D]: prev[r*ld + col + d] <- the left neighbour's last n rows, next[...] <- the right
+ *                            neighbour's first n rows (n*D <= 1024); prev / next untouched at the ends of the sequence */
+typedef struct uuo_comm uuo_comm;
+int uuo_comm_create(int rank, int world, int device, uuo_comm** out);
+int uuo_comm_handle_bytes(void);
+int uuo_comm_export(uuo_comm* c, void* handle_host);
+int uuo_comm_connect(uuo_comm* c, const void* handles_host);
+int uuo_comm_connect_local(uuo_comm* c, uuo_comm* const* peers);
+void uuo_comm_destroy(uuo_comm* c);
+int uuo_comm_all_reduce_sum(uuo_comm* c, float* x, int n, void* stream);
+int uuo_comm_halo_exchange(uuo_comm* c, const float* x, int F, int D, int n, float* prev, float* next, int ld, int col,
+                           void* stream);
+
 /* ---- fused Adam over a flat parameter block (north-star optimiser; torch.optim.Adam semantics) */
 int uuo_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,
                   float beta1, float beta2, float eps, int step, void* stream);

@@ -52,3 +52,13 @@ def rel_err(a, b):
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     return float(np.abs(a - b).max() / max(1e-30, np.abs(b).max()))
+
+
+def frame_rel_err(a, b):
+    """Per-frame-normalised error of [F, ...] arrays: max over frames f of max|a_f - b_f| / max|b_f|.  Stricter than
+    ``rel_err`` (one normaliser for the whole tensor): a frame whose values are small cannot hide behind a large one."""
+    a = np.asarray(a, dtype=np.float64).reshape(np.shape(a)[0], -1)
+    b = np.asarray(b, dtype=np.float64).reshape(np.shape(b)[0], -1)
+    num = np.abs(a - b).max(axis=1)
+    den = np.maximum(np.abs(b).max(axis=1), 1e-30)
+    return float((num / den).max())

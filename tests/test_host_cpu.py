@@ -118,11 +118,31 @@ def _worker(rank, world, port, F, D, out):
         assert torch.equal(nxt, x_all[b:b + 2])
     else:
         assert nxt is None
+    # the persistent-buffer form the closures use (fit.chamfer_closure / marker_closure), with a column offset
+    from uuo_mocap_b200.dist import exchange_halo_into, halo_buffers
+    pbuf, nbuf = halo_buffers(2, D + 3, sh, "cpu")
+    exchange_halo_into(x, 2, sh, pbuf, nbuf, col=3)
+    assert (pbuf is None) == (rank == 0) and (nbuf is None) == (rank == world - 1)
+    if pbuf is not None:
+        assert torch.equal(pbuf[:, 3:], prev) and float(pbuf[:, :3].abs().sum()) == 0.0
+    if nbuf is not None:
+        assert torch.equal(nbuf[:, 3:], nxt)
+    assert not sh.graph_safe                     # torch.distributed transport: the iteration cannot be graph-captured
     loss, g = _temporal_shard(x, prev, nxt, F)
+    if torch.cuda.is_available():                # with a GPU the shard's terms come from the real kernel
+        from uuo_mocap_b200 import _lib
+        from uuo_mocap_b200._lib import check, ptr, stream_ptr
+        xc = x.cuda()
+        pc, nc = (None if t is None else t.cuda().contiguous() for t in (prev, nxt))
+        lk, gk = torch.zeros(1, device="cuda"), torch.zeros_like(xc)
+        check(_lib.lib().uuo_temporal_accumulate(ptr(xc), ptr(pc), ptr(nc), xc.shape[0], D, 1.0 / ((F - 2) * D), ptr(lk),
+                                                 ptr(gk), stream_ptr(xc.device)))
+        assert torch.allclose(gk.cpu(), g, rtol=1e-5, atol=1e-7) and abs(float(lk) - float(loss)) < 1e-6
+        loss, g = lk.cpu()[0], gk.cpu()
     red = torch.zeros(16)
     red[15] = loss
     red[:3] = float(rank + 1)
-    sh.all_reduce_sum_(red)
+    sh.iter_all_reduce_sum_(red)
     cnt = sh.all_reduce_sum(torch.tensor([float(b - a)], dtype=torch.float64))
     ref_loss, ref_g = _temporal_ref(x_all)
     ok = (abs(float(red[15]) - float(ref_loss)) < 1e-6 * abs(float(ref_loss)) and
@@ -219,3 +239,13 @@ def test_resample_prior_matches_reference_loop(img_freq, mocap_freq):
         else:
             assert torch.equal(t[i], trans[frame]) and torch.equal(fc[i], foot[frame])
             assert np.array_equal(got[i], rot[frame].astype(np.float32))
+
+
+def test_lbfgs_is_refused_across_shards():
+    """torch's L-BFGS decides from the rank-local gradient: not defined across frame-range shards (fit._optimise)."""
+    from uuo_mocap_b200.dist import Shard
+    from uuo_mocap_b200.fit import _optimise
+    with pytest.raises(NotImplementedError):
+        _optimise(None, lambda: None, {"num_iters": 5}, {"name": "lbfgs"}, 0.1, None, Shard(0, 2))
+    with pytest.raises(NotImplementedError):       # no name = the reference's optimiser = L-BFGS
+        _optimise(None, lambda: None, {"num_iters": 5}, {}, 0.1, None, Shard(1, 2))

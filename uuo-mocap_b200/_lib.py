@@ -50,6 +50,14 @@ SIGNATURES = {
     "uuo_point_mesh_distance": (_I, [_P, _P, _P, _I, _I, _I, _I, _P, _P]),
     "uuo_profile_enable": (_I, [_I]),
     "uuo_profile_read": (_I, [_I, C.c_char_p, _I, C.POINTER(_F), C.POINTER(_I)]),
+    "uuo_comm_create": (_I, [_I, _I, _I, C.POINTER(_P)]),
+    "uuo_comm_handle_bytes": (_I, []),
+    "uuo_comm_export": (_I, [_P, _P]),
+    "uuo_comm_connect": (_I, [_P, _P]),
+    "uuo_comm_connect_local": (_I, [_P, C.POINTER(_P)]),
+    "uuo_comm_destroy": (None, [_P]),
+    "uuo_comm_all_reduce_sum": (_I, [_P, _P, _I, _P]),
+    "uuo_comm_halo_exchange": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _I, _P]),
     "uuo_adam_step": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _I, _P]),
     "uuo_adam_step_dev": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _P, _P]),
 }

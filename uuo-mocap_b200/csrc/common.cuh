@@ -133,6 +133,16 @@ void uuo_set_error(const char* fmt, ...);
     }                                                                                    \
   } while (0)
 
+// per-device launch configuration (devcfg.cu)
+int uuo_sm_count();                                          // SMs of the current device
+int uuo_sm_count_of(int device);
+int uuo_ensure_dyn_smem(const void* func, size_t bytes);     // opt-in to > 48 KB dynamic smem, once per (device, kernel)
+#define UUO_DYN_SMEM(kernel, bytes)                                        \
+  do {                                                                     \
+    int rc__ = uuo_ensure_dyn_smem((const void*)(kernel), (size_t)(bytes)); \
+    if (rc__) return rc__;                                                 \
+  } while (0)
+
 // per-kernel event timing (prof.cu); a scope records an event before and after the launches inside it
 bool uuo_prof_enabled();
 void uuo_prof_mark(const char* name, cudaStream_t st);

@@ -197,9 +197,9 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
 }
 __global__ void adam_count_kernel(int32_t* step_counter) { *step_counter += 1; }
 
-static inline int nblocks(size_t n, int cap = 148 * 8) {
-  size_t b = (n + 255) / 256;
-  return (int)(b < 1 ? 1 : (b > (size_t)cap ? cap : b));
+static inline int nblocks(size_t n) {
+  const size_t b = (n + 255) / 256, cap = (size_t)uuo_sm_count() * 8;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
 extern "C" int uuo_marker_mask(const float* markers, int n, float* mask, void* stream) {

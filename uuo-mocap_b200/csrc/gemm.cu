@@ -7,6 +7,7 @@
 
 #include "common.cuh"
 
+#ifdef UUO_DEBUG_SIMT   // exact-fp32 SIMT cross-check of the tensor-core GEMMs: debug builds only (tools/gemm_check.py)
 template <int TM, int TN>
 __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ Amat, int lda, int M,
                                                     const float* __restrict__ Bm, int ldb, int Kchunk,
@@ -125,7 +126,19 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ Am
   }
 }
 
-// UUO_GEMM_SIMT=1 selects the exact-fp32 SIMT kernels above (debug cross-check of the tensor-core path)
+#endif  // UUO_DEBUG_SIMT
+
+// The release library has ONE GEMM path (tcgen05).  A build with -DUUO_DEBUG_SIMT keeps the SIMT kernels above and
+// lets UUO_GEMM_SIMT=1 select them per call (debug cross-check of the tensor-core path).
+#ifndef UUO_DEBUG_SIMT
+int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+  return launch_vposed_gemm_umma(m, F, ws, st);
+}
+int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st) {
+  *n_parts = uuo_gcoef_splits(m, F);
+  return launch_gcoef_gemm_umma(m, F, ws, st);
+}
+#else
 static bool use_simt() {
   const char* e = getenv("UUO_GEMM_SIMT");   // read per call so one process can compare both paths
   return e && e[0] == '1';
@@ -156,3 +169,4 @@ int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts,
   } UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
+#endif  // UUO_DEBUG_SIMT

@@ -245,11 +245,7 @@ extern "C" int uuo_point_mesh_distance(const float* points, const float* vertice
   if (F == 0 || M == 0) return UUO_OK;
   const size_t smem = (size_t)((3 * V + 3) & ~3) * 4 + (size_t)M * 4 + (size_t)3 * M * 4;
   UUO_CHECK_ARG(smem <= 227 * 1024, "V / M too large for the shared-memory frame");
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    UUO_CUDA(cudaFuncSetAttribute(point_mesh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  UUO_DYN_SMEM(point_mesh_kernel, smem);
   ProfScope ps_("point_mesh_distance", (cudaStream_t)stream);
   point_mesh_kernel<<<F, 256, smem, (cudaStream_t)stream>>>(points, vertices, faces, F, M, V, NF, dist);
   UUO_LAUNCH_CHECK();

@@ -240,17 +240,8 @@ extern "C" int uuo_nn_argmin_ordered(const float* markers, const float* vertices
   if (!order || V > 65535 || L.nr > 32 || smem > 227 * 1024)      // no order / does not fit: the exhaustive kernel
     return uuo_nn_argmin(markers, vertices, F, M, V, dist2, idx, stream);
   if (F == 0 || M == 0) return UUO_OK;
-  static thread_local size_t configured = 0;
-  static thread_local int n_sm = 0;
-  if (smem > configured) {
-    UUO_CUDA(cudaFuncSetAttribute(nn_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  if (!n_sm) {
-    int dev = 0;
-    UUO_CUDA(cudaGetDevice(&dev));
-    UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-  }
+  UUO_DYN_SMEM(nn_tiles_kernel, smem);
+  const int n_sm = uuo_sm_count();
   {
     // one persistent CTA per SM; warps = markers / passes so that every pass over the markers is (almost) full
     const int passes = (M + 31) / 32;
@@ -563,17 +554,8 @@ static int nn_presorted_launch(const float* markers, const float* vertices, cons
                 "V too large for the presorted correspondence kernel (two staged frames must fit in shared memory)");
   if (F == 0 || M == 0) return UUO_OK;                     // empty inputs: nothing to read, pointers may be NULL
   UUO_CHECK_ARG(markers && vertices && dist2 && idx, "NULL pointer");
-  static thread_local size_t configured = 0;
-  static thread_local int n_sm = 0;
-  if (L.total > configured) {
-    UUO_CUDA(cudaFuncSetAttribute(nn_presorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-    configured = L.total;
-  }
-  if (!n_sm) {
-    int dev = 0;
-    UUO_CUDA(cudaGetDevice(&dev));
-    UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-  }
+  UUO_DYN_SMEM(nn_presorted_kernel, L.total);
+  const int n_sm = uuo_sm_count();
   {
     ProfScope ps_("nn_argmin_presorted", (cudaStream_t)stream);
     nn_presorted_kernel<<<F < n_sm ? F : n_sm, NP_THREADS, L.total, (cudaStream_t)stream>>>(markers, vertices, ids, weights,

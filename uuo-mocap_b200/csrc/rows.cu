@@ -373,17 +373,8 @@ int launch_rows_forward(const uuo_model* m, const float* transl, int F, const in
   const int G = rows_shared > 1 ? rows_shared : 1;           // rows_shared = G > 1: G contiguous frame groups, rows[G][R]
   if (F % G) { uuo_set_error("rows path: F must be a multiple of the number of row groups"); return UUO_ERR_ARG; }
   if (rows_shared && 3 * R <= 32 * ROWSS_NI && L.total <= 227 * 1024 && F / G >= 64) {
-    static thread_local size_t configured = 0;
-    static thread_local int n_sm = 0;
-    if (L.total > configured) {
-      UUO_CUDA(cudaFuncSetAttribute(rows_forward_shared_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
-      configured = L.total;
-    }
-    if (!n_sm) {
-      int dev = 0;
-      UUO_CUDA(cudaGetDevice(&dev));
-      UUO_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    }
+    UUO_DYN_SMEM(rows_forward_shared_kernel, L.total);
+    const int n_sm = uuo_sm_count();
     const int Fg = F / G;
     const int need = (Fg + ROWSS_WARPS * ROWSS_NF - 1) / (ROWSS_WARPS * ROWSS_NF);
     const int per_group = std::max(1, std::min(need, (n_sm + G - 1) / G));

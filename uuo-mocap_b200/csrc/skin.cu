@@ -9,10 +9,15 @@
 
 #include <stdlib.h>
 // UUO_SKIN_SIMT=1 selects the exact-fp32 SIMT kernels (debug cross-check of the tensor-core path, tools/gemm_check.py)
+// (only in a build with -DUUO_DEBUG_SIMT; the release library has one skinning path, the SIMT kernels are compiled out)
+#ifdef UUO_DEBUG_SIMT
 static bool skin_simt() {
   const char* e = getenv("UUO_SKIN_SIMT");
   return e && e[0] == '1';
 }
+#else
+static constexpr bool skin_simt() { return false; }
+#endif
 
 // number of d(A) partial slabs launch_skin_backward writes to ws.gA
 int uuo_ga_parts(const uuo_model* m, bool with_g_joints) {
@@ -24,6 +29,7 @@ int uuo_ga_parts(const uuo_model* m, bool with_g_joints) {
 #define SK_VPT 2
 #define SK_FB 16
 
+#ifdef UUO_DEBUG_SIMT
 __global__ void __launch_bounds__(SK_THREADS) skin_forward_kernel(
     const float* __restrict__ W, const float* __restrict__ A, const float* __restrict__ vposed, int NP,
     const float* __restrict__ transl, int F, int V, float* __restrict__ vertices) {
@@ -90,6 +96,7 @@ __global__ void __launch_bounds__(SK_THREADS) skin_forward_kernel(
     }
   }
 }
+#endif  // UUO_DEBUG_SIMT
 
 // joints[f, J+e] = vertices[f, extra_ids[e]]   (vertex_joint_selector.py:73-80; transl already inside)
 __global__ void extra_joints_kernel(const float* __restrict__ vertices, const int32_t* __restrict__ extra_ids,
@@ -121,6 +128,7 @@ __device__ __forceinline__ void load_g(const float* __restrict__ g_vertices, con
 }
 
 // g_vposed[f,v] = T[:3,:3]^T g[f,v]
+#ifdef UUO_DEBUG_SIMT
 __global__ void __launch_bounds__(SK_THREADS) skin_backward_vposed_kernel(
     const float* __restrict__ W, const float* __restrict__ A, const float* __restrict__ g_vertices,
     const float* __restrict__ g_joints, const int32_t* __restrict__ extra_ids, const uint8_t* __restrict__ vflag,
@@ -273,6 +281,7 @@ __global__ void __launch_bounds__(GA_THREADS) skin_backward_A_kernel(
     if (jg == 0) *reinterpret_cast<float4*>(dst + 288) = make_float4(gsum[0], gsum[1], gsum[2], 0.f);
   }
 }
+#endif  // UUO_DEBUG_SIMT
 
 // ---- extra-joint rows of g_joints (vertex_joint_selector.py:73-80): joints[J+e] = vertices[extra_ids[e]], so their
 // upstream gradient lands on NU <= NE distinct vertices.  The tensor-core kernels see g_vertices only; these two tiny
@@ -342,13 +351,16 @@ int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* v
     int rc;
     { ProfScope ps_("pack_transforms", st); if ((rc = launch_pack_transforms(m, F, ws, st))) return rc; }
     { ProfScope ps_("skin_forward", st); if ((rc = launch_skin_tc(m, 0, F, ws.vposed, nullptr, transl, vertices, ws, st))) return rc; }
-  } else {
+  }
+#ifdef UUO_DEBUG_SIMT
+  else {
   const int vpb = SK_THREADS * SK_VPT;
   dim3 grid((m->V + vpb - 1) / vpb, (F + SK_FB - 1) / SK_FB);
   { ProfScope ps_("skin_forward", st);
   skin_forward_kernel<<<grid, SK_THREADS, 0, st>>>(m->W, ws.A, ws.vposed, m->NP, transl, F, m->V, vertices);
   } UUO_LAUNCH_CHECK();
   }
+#endif
   if (joints && m->NE > 0) {
     int n = F * m->NE;
     extra_joints_kernel<<<(n + 255) / 256, 256, 0, st>>>(vertices, m->extra_ids, F, m->V, m->J, m->NE, joints);
@@ -359,9 +371,6 @@ int launch_skin_forward(const uuo_model* m, const float* transl, int F, float* v
 
 int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, const float* g_joints,
                          const uuo_ws& ws, cudaStream_t st) {
-  const int vpb = SK_THREADS * SK_VPT;
-  // cover every column of the padded row so the pad is written as zeros
-  dim3 grid1((m->NP / 3 + 1 + vpb - 1) / vpb, (F + SK_FB - 1) / SK_FB);
   if (!skin_simt()) {
     int rc;
     ProfScope ps_("skin_backward_vposed", st);
@@ -372,10 +381,17 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
                                                             m->NU, m->J, m->NE, m->NP, ws.gvposed);
       UUO_LAUNCH_CHECK();
     }
-  } else { ProfScope ps_("skin_backward_vposed", st);
+  }
+#ifdef UUO_DEBUG_SIMT
+  else { ProfScope ps_("skin_backward_vposed", st);
+  const int vpb = SK_THREADS * SK_VPT;
+  // cover every column of the padded row so the pad is written as zeros
+  dim3 grid1((m->NP / 3 + 1 + vpb - 1) / vpb, (F + SK_FB - 1) / SK_FB);
   skin_backward_vposed_kernel<<<grid1, SK_THREADS, 0, st>>>(m->W, ws.A, g_vertices, g_joints, m->extra_ids, m->vflag,
                                                             F, m->V, m->NE, m->NP, ws.gvposed);
-  } UUO_LAUNCH_CHECK();
+  }
+#endif
+  UUO_LAUNCH_CHECK();
   if (!skin_simt()) {
     ProfScope ps_("skin_backward_A", st);
     int rc = launch_skin_bwdA_tc(m, F, g_vertices, g_joints, ws, st);
@@ -389,11 +405,13 @@ int launch_skin_backward(const uuo_model* m, int F, const float* g_vertices, con
     }
     return UUO_OK;
   }
+#ifdef UUO_DEBUG_SIMT
   const int vps = ((m->V + UUO_NSPLIT_GA - 1) / UUO_NSPLIT_GA + GA_VC - 1) / GA_VC * GA_VC;
   dim3 grid2((F + GA_FB - 1) / GA_FB, UUO_NSPLIT_GA);
   { ProfScope ps_("skin_backward_A", st);
   skin_backward_A_kernel<<<grid2, GA_THREADS, 0, st>>>(m->W, ws.vposed, g_vertices, g_joints, m->extra_ids, F, m->V,
                                                        m->NE, m->NP, vps, ws.gA);
   } UUO_LAUNCH_CHECK();
+#endif
   return UUO_OK;
 }

@@ -277,15 +277,8 @@ int uuo_bwdA_splits(const uuo_model* m) {
 
 int launch_skin_bwdA_tc(const uuo_model* m, int F, const float* g_vertices, const float* g_joints, const uuo_ws& ws,
                         cudaStream_t st) {
-  static bool attr_set = false;
-  static int num_sms = 148;
-  if (!attr_set) {
-    UUO_CUDA(cudaFuncSetAttribute(skin_bwdA_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    int dev = 0;
-    UUO_CUDA(cudaGetDevice(&dev));
-    UUO_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    attr_set = true;
-  }
+  UUO_DYN_SMEM(skin_bwdA_tc_kernel, SMEM_BYTES);
+  const int num_sms = uuo_sm_count();
   BwdAArgs a;
   a.WTimg = m->WTimg; a.vposed = ws.vposed; a.g_vertices = g_vertices; a.g_joints = g_joints;
   a.extra_ids = m->extra_ids; a.vflag = m->vflag; a.gA = ws.gA;

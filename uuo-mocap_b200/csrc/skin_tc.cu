@@ -263,16 +263,9 @@ int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStre
 
 int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const float* g_joints, const float* transl,
                    float* out, const uuo_ws& ws, cudaStream_t st) {
-  static bool attr_set = false;
-  static int num_sms = 148;
-  if (!attr_set) {
-    UUO_CUDA(cudaFuncSetAttribute(skin_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    UUO_CUDA(cudaFuncSetAttribute(skin_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    int dev = 0;
-    UUO_CUDA(cudaGetDevice(&dev));
-    UUO_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    attr_set = true;
-  }
+  UUO_DYN_SMEM(skin_tc_kernel<0>, SMEM_BYTES);
+  UUO_DYN_SMEM(skin_tc_kernel<1>, SMEM_BYTES);
+  const int num_sms = uuo_sm_count();
   SkinArgs a;
   a.Wimg = m->Wimg; a.Aimg = ws.Aimg; a.in = in; a.g_joints = g_joints; a.extra_ids = m->extra_ids; a.vflag = m->vflag;
   a.transl = transl; a.out = out;

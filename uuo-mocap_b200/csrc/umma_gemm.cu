@@ -280,18 +280,10 @@ void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int 
     }
 }
 
-static int g_num_sms = 0;
 static int launch_umma(const GemmArgs& g, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    UUO_CUDA(cudaFuncSetAttribute(umma_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    int dev = 0;
-    UUO_CUDA(cudaGetDevice(&dev));
-    UUO_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    attr_set = true;
-  }
+  UUO_DYN_SMEM(umma_gemm_kernel, SMEM_BYTES);
   const int items = g.m_tiles * g.n_tiles * g.k_splits;
-  umma_gemm_kernel<<<std::min(items, g_num_sms), NTHREADS, SMEM_BYTES, st>>>(g);
+  umma_gemm_kernel<<<std::min(items, uuo_sm_count()), NTHREADS, SMEM_BYTES, st>>>(g);
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
@@ -299,7 +291,7 @@ static int launch_umma(const GemmArgs& g, cudaStream_t st) {
 // number of deterministic K-split slabs the backward GEMM writes for F frames (<= UUO_NSPLIT_GC)
 int uuo_gcoef_splits(const uuo_model* m, int F) {
   const int m_tiles = (F + BM - 1) / BM, kbT = m->NP / BK;
-  int want = std::max(1, std::min(UUO_NSPLIT_GC, (2 * 148 + m_tiles - 1) / m_tiles));
+  int want = std::max(1, std::min(UUO_NSPLIT_GC, (2 * uuo_sm_count_of(m->device) + m_tiles - 1) / m_tiles));
   const int per = (kbT + want - 1) / want;
   return (kbT + per - 1) / per;
 }

@@ -30,7 +30,7 @@ import torch
 
 from . import _lib, ops
 from ._lib import check, ptr, stream_ptr
-from .dist import Shard, exchange_halo
+from .dist import Shard, exchange_halo_into, halo_buffers
 from .smpl import POSE_RAW6D, SMPL, SmplInference
 
 MARKER_DISTANCE = ops.MARKER_DISTANCE
@@ -44,7 +44,8 @@ class FitProblem:
     """Device buffers of one shard of one sequence (or of H hypotheses stacked along the frame axis)."""
 
     def __init__(self, smpl_inference, markers: torch.Tensor, o_pose_body: torch.Tensor, o_betas: torch.Tensor,
-                 shard: Optional[Shard] = None, groups: int = 1):
+                 shard: Optional[Shard] = None, groups: int = 1, F_global: Optional[int] = None,
+                 wsum_global: Optional[float] = None):
         self.smpl = _model_of(smpl_inference)
         self.mh = self.smpl.handle
         dev = self.mh.device
@@ -59,9 +60,12 @@ class FitProblem:
         self.o_betas = o_betas.to(dev, torch.float32).reshape(-1, self.mh.NB).contiguous()
         self.mask = ops.get_marker_mask(self.markers)
         # global normalisers (src/video_mocap/losses/chamfer_distance.py:20 divides by sum(weights))
-        fg = torch.tensor([float(self.F // groups), float(self.mask.sum().item()) / groups], dtype=torch.float64)
-        fg = self.shard.all_reduce_sum(fg)
-        self.F_global, self.wsum_global = int(fg[0].item()), float(fg[1].item())
+        # (a caller that drives several shards from one process passes them in: tests/test_shard_gpu.py)
+        if F_global is None or wsum_global is None:
+            fg = torch.tensor([float(self.F // groups), float(self.mask.sum().item()) / groups], dtype=torch.float64)
+            fg = self.shard.all_reduce_sum(fg)
+            F_global, wsum_global = int(fg[0].item()), float(fg[1].item())
+        self.F_global, self.wsum_global = int(F_global), float(wsum_global)
         self.ws = self.mh.workspace(self.F)
         self.vertices = None
         # dense forward of the chamfer stage runs on the visiting-order twin (rows of `vertices` are renumbered,
@@ -72,9 +76,16 @@ class FitProblem:
         self.d2 = torch.empty((self.F, self.M), dtype=torch.float32, device=dev)
         self.g_rows = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
         self.virt = torch.empty((self.F, self.M, 3), dtype=torch.float32, device=dev)
-        self.red = torch.zeros(16, dtype=torch.float32, device=dev)       # [d/d betas (<=10) | pad | loss @ 15]
+        # one row per hypothesis group: [d/d betas (<=10) | pad | .]; the loss of the whole problem sits at [0, 15].
+        # This block is what the shards sum every iteration (<= 1024 floats).
+        if groups * 16 > 1024:
+            raise ValueError("at most 64 stacked hypotheses per problem")
+        self.red = torch.zeros((groups, 16), dtype=torch.float32, device=dev)
+        self.loss_slot = self.red.view(-1)[15:16]
         self.gbetas_rows = None
         self.mm = None                                     # per-frame marker mean (trans_vel)
+        self.tv_halo = None                                # (prev, next) [1,6] = [trans | marker mean] of the neighbour frame
+        self.tp_halo = None                                # (prev, next) [2,D] pose rows of the neighbours (temporal)
         self.n_closure = 0
 
     # -- thin C-ABI call helpers -------------------------------------------------------------
@@ -113,7 +124,7 @@ class FitProblem:
                                                ptr(g_yaw), ptr(g_trans), self._st()))
 
     def sqdiff(self, x, y, scale, g):
-        check(_lib.lib().uuo_sqdiff_accumulate(ptr(x), ptr(y), x.numel(), float(scale), ptr(self.red[15:]), ptr(g),
+        check(_lib.lib().uuo_sqdiff_accumulate(ptr(x), ptr(y), x.numel(), float(scale), ptr(self.loss_slot), ptr(g),
                                                self._st()))
 
     def betas_rows(self, betas):
@@ -123,13 +134,13 @@ class FitProblem:
         return torch.repeat_interleave(betas.reshape(self.groups, -1), self.F // self.groups, dim=0).contiguous()
 
     def reduce_gbetas(self, g_betas_param):
-        """d/d betas: (a) stacked hypotheses: per-frame rows -> per-group sums; (b) all-reduce over shards."""
-        if self.groups > 1:
-            g_betas_param.copy_(self.gbetas_rows.view(self.groups, self.F // self.groups, -1).sum(1))
-            return
+        """d/d betas and the loss: (a) stacked hypotheses: per-frame rows -> one row per group; (b) ONE sum over the
+        shards of the [G,16] block (peer-memory kernel when the shard has a PeerComm, else torch.distributed)."""
         nb = self.mh.NB
-        self.shard.all_reduce_sum_(self.red)               # one 16-float all-reduce: d betas + loss
-        g_betas_param.copy_(self.red[:nb].view_as(g_betas_param))
+        if self.groups > 1:
+            self.red[:, :nb] = self.gbetas_rows.view(self.groups, self.F // self.groups, -1).sum(1)
+        self.shard.iter_all_reduce_sum_(self.red)
+        g_betas_param.copy_(self.red[:, :nb].reshape(g_betas_param.shape))
 
     def gbetas_target(self):
         if self.groups == 1:
@@ -181,7 +192,7 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
                                                          ptr(prob.mask), ptr(prob.pos), F, M, prob.mh.V, ptr(prob.d2),
                                                          ptr(prob.idx), ptr(prob.pos), prob._st()))
             check(_lib.lib().uuo_chamfer_rows(ptr(prob.markers), ptr(verts), ptr(prob.mask), ptr(prob.pos), F, M,
-                                              prob.mh.V, w_ch / prob.wsum_global, ptr(prob.red[15:]), ptr(prob.g_rows),
+                                              prob.mh.V, w_ch / prob.wsum_global, ptr(prob.loss_slot), ptr(prob.g_rows),
                                               prob._st()))
         else:
             prob.g_rows.zero_()
@@ -198,19 +209,19 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
             if prob.mm is None:
                 prob.mm = torch.empty((F, 3), dtype=torch.float32, device=prob.dev)
                 check(_lib.lib().uuo_marker_mean(ptr(prob.markers), F, M, ptr(prob.mm), prob._st()))
-            halo_src = torch.cat([v["trans"], prob.mm], dim=1)                          # [F,6]
-            prev, nxt = exchange_halo(halo_src, 1, prob.shard)
+                prob.tv_halo = halo_buffers(1, 6, prob.shard, prob.dev)
+                exchange_halo_into(prob.mm, 1, prob.shard, *prob.tv_halo, col=3)        # constant: sent once
+            prev, nxt = prob.tv_halo
+            exchange_halo_into(v["trans"], 1, prob.shard, prev, nxt, col=0)
             check(_lib.lib().uuo_transvel_accumulate(ptr(v["trans"]), ptr(prob.mm), ptr(prev), ptr(nxt), F,
-                                                     losses["trans_vel"] / ((Fg - 1) * 3), ptr(prob.red[15:]),
+                                                     losses["trans_vel"] / ((Fg - 1) * 3), ptr(prob.loss_slot),
                                                      ptr(g["trans"]), prob._st()))
         prob.reduce_gbetas(g["betas"])
-        if prob.groups > 1:
-            prob.shard.all_reduce_sum_(prob.red)
         if "reg_betas" in losses:                                                       # :255-256 (same on every rank)
             ob = prob.o_betas.expand_as(v["betas"]).contiguous()
             prob.sqdiff(v["betas"], ob, losses["reg_betas"] / v["betas"][0].numel(), g["betas"])
     prob.n_closure += 1
-    return prob.red[15]
+    return prob.loss_slot[0]
 
 
 def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, losses: Dict[str, float]) -> torch.Tensor:
@@ -231,7 +242,7 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
         virt = prob.lbs_forward_rows(brows, v["root_orient"], v["pose_body"], None, v["trans"], vertex_idx, shared)
         if "marker" in losses:                                                          # :356-362 (mean over ALL F*M)
             check(_lib.lib().uuo_marker_loss_rows(ptr(prob.markers), ptr(virt), ptr(prob.mask), F * M, MARKER_DISTANCE,
-                                                  losses["marker"] / (Fg * M), ptr(prob.red[15:]), ptr(prob.g_rows),
+                                                  losses["marker"] / (Fg * M), ptr(prob.loss_slot), ptr(prob.g_rows),
                                                   prob._st()))
         else:
             prob.g_rows.zero_()
@@ -245,18 +256,19 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
                 raise ValueError("the temporal term is not defined across stacked hypotheses")
             D = v["pose_body"][0].numel()
             x = v["pose_body"].view(F, D)
-            prev, nxt = exchange_halo(x, 2, prob.shard)
+            if prob.tp_halo is None:
+                prob.tp_halo = halo_buffers(2, D, prob.shard, prob.dev)
+            prev, nxt = prob.tp_halo
+            exchange_halo_into(x, 2, prob.shard, prev, nxt)
             check(_lib.lib().uuo_temporal_accumulate(ptr(x), ptr(prev), ptr(nxt), F, D,
-                                                     losses["temporal"] / ((Fg - 2) * D), ptr(prob.red[15:]),
+                                                     losses["temporal"] / ((Fg - 2) * D), ptr(prob.loss_slot),
                                                      ptr(g["pose_body"]), prob._st()))
         prob.reduce_gbetas(g["betas"])
-        if prob.groups > 1:
-            prob.shard.all_reduce_sum_(prob.red)
         if "reg_betas" in losses:                                                       # :366-367
             ob = prob.o_betas.expand_as(v["betas"]).contiguous()
             prob.sqdiff(v["betas"], ob, losses["reg_betas"] / v["betas"][0].numel(), g["betas"])
     prob.n_closure += 1
-    return prob.red[15]
+    return prob.loss_slot[0]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -264,18 +276,20 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
 # ------------------------------------------------------------------------------------------------
 def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int, lr: float,
              betas=(0.9, 0.999), eps: float = 1e-8, on_iter: Optional[Callable] = None,
-             graph: Optional[bool] = None, warm: int = 3) -> Optional[torch.Tensor]:
+             graph: Optional[bool] = None, warm: int = 3, shard: Optional[Shard] = None) -> Optional[torch.Tensor]:
     """closure -> fused Adam over the flat block.  No host synchronisation inside the loop unless ``on_iter`` asks
     for the loss.  After ``warm`` eager iterations ONE iteration (every kernel of the closure + the update, ~20-35
     launches) is captured in a CUDA graph and replayed for the rest: the step number lives in device memory
     (uuo_adam_step_dev), so nothing on the host changes between iterations.  ``graph=None``: on unless a callback
-    wants the loss, the per-kernel profiler is running, or the closure talks to other ranks."""
+    wants the loss, the per-kernel profiler is running, or the closure's exchange with the other shards is issued
+    from the host (``shard.graph_safe`` is False: torch.distributed transport instead of the peer-memory kernels)."""
     m = torch.zeros_like(pb.flat)
     v = torch.zeros_like(pb.flat)
     counter = torch.zeros(1, dtype=torch.int32, device=pb.flat.device)
+    multi = torch.distributed.is_available() and torch.distributed.is_initialized()
     if graph is None:
-        graph = on_iter is None and not ops.PROFILING[0] and not (torch.distributed.is_available()
-                                                                  and torch.distributed.is_initialized())
+        safe = shard.graph_safe if shard is not None else not multi
+        graph = on_iter is None and not ops.PROFILING[0] and safe
     loss = None
 
     def one():
@@ -294,7 +308,8 @@ def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int
         dev = pb.flat.device
         g = torch.cuda.CUDAGraph()
         with torch.cuda.device(dev):
-            with torch.cuda.graph(g):
+            # thread_local: NCCL's watchdog thread may touch the CUDA API while this thread captures
+            with torch.cuda.graph(g, capture_error_mode="thread_local" if multi else "global"):
                 loss = one()
             while it < num_iters:        # the capture itself executed nothing
                 g.replay()
@@ -323,14 +338,22 @@ def run_lbfgs(pb: ParamBlock, closure: Callable[[], torch.Tensor], max_iter: int
     return n[0]
 
 
-def _optimise(pb, closure, stage_cfg, opt_cfg, lbfgs_lr, on_iter=None):
-    name = str(opt_cfg.get("name", "adam")).lower()
+def _optimise(pb, closure, stage_cfg, opt_cfg, lbfgs_lr, on_iter=None, shard: Optional[Shard] = None):
+    """``optimizer.name``: "lbfgs" (the reference's optimiser and the default when the yaml names none, like
+    config/video_mocap.yaml) or "adam" (the fused north-star optimiser: ``default_config`` selects it)."""
+    name = str(opt_cfg.get("name", "lbfgs")).lower()
     iters = int(stage_cfg["num_iters"])
     if iters <= 0:
         return
     if name == "adam":
-        run_adam(pb, closure, iters, float(stage_cfg.get("lr_adam", opt_cfg.get("lr", 0.01))), on_iter=on_iter)
+        run_adam(pb, closure, iters, float(stage_cfg.get("lr_adam", opt_cfg.get("lr", 0.01))), on_iter=on_iter,
+                 shard=shard)
     elif name == "lbfgs":
+        if shard is not None and shard.world > 1:
+            # torch's L-BFGS takes its direction, line-search and stopping decisions from the rank-local flat
+            # gradient: shards would step the shared betas differently and call the closure's collectives a
+            # different number of times.  Only the fused Adam path is defined across shards.
+            raise NotImplementedError("optimizer.name = 'lbfgs' is not defined across frame-range shards; use 'adam'")
         run_lbfgs(pb, closure, iters, lbfgs_lr, float(opt_cfg.get("tolerance_grad", 1e-7)),
                   float(opt_cfg.get("tolerance_change", 1e-9)))
     else:
@@ -407,7 +430,7 @@ def optim_chamfer(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
         def cb(it, loss):
             if verbose:
                 print("Chamfer", it, float(loss))
-    _optimise(pb, closure, st, config.get("optimizer", {}), 0.1, cb)
+    _optimise(pb, closure, st, config.get("optimizer", {}), 0.1, cb, prob.shard)
     with torch.no_grad():
         trans.copy_(pb.views["trans"])
         betas.copy_(pb.views["betas"].view_as(betas))
@@ -440,7 +463,7 @@ def optim_markers(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
     cb = None
     if verbose:
         cb = lambda it, loss: print("Marker", it, float(loss))
-    _optimise(pb, closure, st, config.get("optimizer", {}), 1.0, cb)
+    _optimise(pb, closure, st, config.get("optimizer", {}), 1.0, cb, prob.shard)
     with torch.no_grad():
         pose_body.copy_(pb.views["pose_body"])
         betas.copy_(pb.views["betas"].view_as(betas))
@@ -505,8 +528,19 @@ def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient,
     root = (rot_z(ang.view(H, 1, 1, 1)) @ T(root_orient).unsqueeze(0)).reshape(H * F, 1, 3, 3).contiguous()   # :465
     bet = T(betas).reshape(1, -1).repeat(H, 1).contiguous()
     obet = T(o_betas).reshape(1, -1)
+    lbfgs = str(config.get("optimizer", {}).get("name", "lbfgs")).lower() == "lbfgs"
+    if lbfgs and H > 1:
+        # the reference runs an independent L-BFGS per hypothesis (its own line search and stopping test); one stacked
+        # problem would couple them through the flat vector, so fit them one after another and merge
+        parts = [fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient, trans, img_mask,
+                                smpl_inference, config, [a], shard) for a in angles]
+        scores = [p[1][0] for p in parts]
+        fitted = [p[2][0] for p in parts]
+        return int(np.argmin(scores)), scores, fitted
     prob = FitProblem(smpl, mk, opose, obet, shard, groups=H)
     optim_chamfer(mk, pose, opose, bet, obet, root, tr, None, None, smpl, config, problem=prob, groups=H)
+    chamfer_snap = {"pose_body": normalize_rot(pose).clone(), "root_orient": normalize_rot(root).clone(),
+                    "trans": tr.clone(), "betas": bet.clone()}                                                  # :497-503
     # correspondences per hypothesis (they do not mix frames of different hypotheses)
     vidx = []
     for h in range(H):
@@ -521,15 +555,18 @@ def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient,
     scores, fitted = [], []
     for h in range(H):
         sl = slice(h * F, (h + 1) * F)
-        p = {"pose_body": pose[sl].clone(), "betas": bet[h:h + 1].clone(), "root_orient": root[sl].clone(),
-             "trans": tr[sl].clone()}
-        out = smpl(betas=p["betas"], body_pose=normalize_rot(p["pose_body"]), global_orient=normalize_rot(p["root_orient"]),
-                   transl=p["trans"], pose2rot=False)
-        val, _ = weighted_chamfer_distance(mk[sl], out.vertices, ops.get_marker_mask(mk[sl]))
-        tot = torch.stack([val * float(ops.get_marker_mask(mk[sl]).sum()), ops.get_marker_mask(mk[sl]).sum()]).double().cpu()
+        # the reference carries the 6D-normalised rotations on from here (multimodal.py:566-574, 601-606)
+        p = {"pose_body": normalize_rot(pose[sl]).clone(), "betas": bet[h:h + 1].clone(),
+             "root_orient": normalize_rot(root[sl]).clone(), "trans": tr[sl].clone()}
+        out = smpl(betas=p["betas"], body_pose=p["pose_body"], global_orient=p["root_orient"], transl=p["trans"],
+                   pose2rot=False)
+        wmask = ops.get_marker_mask(mk[sl])
+        val, _ = weighted_chamfer_distance(mk[sl], out.vertices, wmask)
+        tot = torch.stack([val * wmask.sum(), wmask.sum()]).double().cpu()
         tot = (shard or Shard()).all_reduce_sum(tot)
         scores.append(float(tot[0] / tot[1]) if float(tot[1]) > 0 else 0.0)
         p["vertex_idx"] = vidx[h]
+        p["chamfer"] = {k: (v[sl] if k != "betas" else v[h:h + 1]).clone() for k, v in chamfer_snap.items()}
         fitted.append(p)
     best = int(np.argmin(scores))
     return best, scores, fitted

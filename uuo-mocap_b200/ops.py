@@ -109,6 +109,10 @@ def mean_distance_argmin(markers: torch.Tensor, vertices: torch.Tensor, frame_ma
     if acc is None:
         acc = torch.zeros((M, V), dtype=torch.float32, device=dev)
     fm = _req(frame_mask, "frame_mask") if frame_mask is not None else None
+    if fm is not None and fm.numel() != F:
+        raise ValueError("frame_mask must hold one entry per frame (%d), got %d" % (F, fm.numel()))
+    if vertices.shape[0] != F:
+        raise ValueError("markers and vertices must have the same number of frames")
     with torch.cuda.device(dev):
         check(_lib.lib().uuo_mean_dist_accumulate(ptr(markers), ptr(vertices), ptr(fm), F, M, V, ptr(acc),
                                                   stream_ptr(dev)))

@@ -31,16 +31,29 @@ def fit_capture(markers: torch.Tensor, pose_body: torch.Tensor, betas: torch.Ten
     smpl = fit._model_of(smpl_inference)
     dev = smpl.device
     if img_frame_rate is not None and img_frame_rate != mocap_frame_rate:
+        n_src = torch.as_tensor(trans).shape[0]
         trans, root_orient, pose_body, _ = resample_prior(torch.as_tensor(trans), torch.as_tensor(root_orient),
                                                           torch.as_tensor(pose_body), torch.as_tensor(trans),
                                                           img_frame_rate, mocap_frame_rate)
+        if img_mask is not None:
+            # the mask follows the prior to the marker rate: output frame i reads source frame int(i * img / mocap), the
+            # frame resample_prior starts its blend from (the reference leaves the mask at the video rate, which only
+            # lines up when the rates agree)
+            im = torch.as_tensor(img_mask).reshape(-1)
+            if im.shape[0] != n_src:
+                raise ValueError("img_mask must have one entry per frame of the video prior")
+            src = torch.tensor([min(int(i * (img_frame_rate / mocap_frame_rate)), n_src - 1)
+                                for i in range(trans.shape[0])], dtype=torch.long, device=im.device)
+            img_mask = im[src]
     T = lambda t: torch.as_tensor(t).detach().to(dev, torch.float32).contiguous()
     mk = torch.nan_to_num(T(markers), nan=0.0)                                          # :188
     F = min(mk.shape[0], trans.shape[0])                                                # :191-199
     mk, o_pose, o_betas = mk[:F].contiguous(), T(pose_body)[:F].contiguous(), T(betas).reshape(1, -1)
     root, tr = T(root_orient)[:F].clone(), T(trans)[:F].clone()
     bet = o_betas.clone()
-    mask = torch.ones(F, device=dev) if img_mask is None else T(img_mask)[:F]
+    mask = torch.ones(F, device=dev) if img_mask is None else T(img_mask).reshape(-1)[:F].contiguous()
+    if mask.shape[0] != F:
+        raise ValueError("img_mask holds %d frames, the capture %d" % (mask.shape[0], F))
     snap = lambda p: {k: v.detach().cpu().numpy() for k, v in p.items()}
     stages = {}
 
@@ -56,9 +69,12 @@ def fit_capture(markers: torch.Tensor, pose_body: torch.Tensor, betas: torch.Ten
     best, scores, fitted = fit.fit_hypotheses(mk, o_pose.clone(), o_pose, bet, o_betas, root, tr, mask, smpl, config, angles)
     p = fitted[best]                                                                    # :601-608
     pose, root, tr, bet = p["pose_body"], p["root_orient"], p["trans"], p["betas"]
+    if config["stages"]["chamfer"]["num_iters"] > 0:                                    # :497-503 (test/test.py:131-143)
+        c = p["chamfer"]
+        stages["chamfer"] = snap({"trans": c["trans"], "root_orient": c["root_orient"], "betas": c["betas"][0],
+                                  "pose_body": c["pose_body"]})
     if config["stages"]["marker"]["num_iters"] > 0:
-        stages["marker"] = snap({"trans": tr, "root_orient": fit.normalize_rot(root), "betas": bet[0],
-                                 "pose_body": fit.normalize_rot(pose)})
+        stages["marker"] = snap({"trans": tr, "root_orient": root, "betas": bet[0], "pose_body": pose})
 
     labels_out = marker_labels
     for _ in range(int(config.get("stage_repeats", 0))):                                # :610-678
