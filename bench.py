@@ -1,17 +1,24 @@
 #!/usr/bin/env python
-"""bench.py -- frame-iterations/s of the SMPL lbs() forward+backward hot path (BASELINE.json configs[1]).
+"""bench.py -- frame-iterations/s of SMPL marker fitting (BASELINE.json `metric`) on N GPUs of one node.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload fit100k|fit5k|mht|lbs] [--impl ours|reference]
 
-One "step" = one pass of lbs() forward + backward over a batch of F synthetic frames per GPU
-(weak scaling: frames are independent, ranks never communicate on the data path).
-  value : device-resident inputs, direct C-ABI calls, CUDA-event timed, max over ranks
-  e2e   : the public API (SMPL.forward + autograd backward fed the upstream gradients) with pinned HOST parameters
-          copied in and the parameter gradients + a scalar copied out inside the timed region
-  roofline : dominant kernel of the step, timed live with CUDA events inside the library
-  cpu_baseline : the oracle (bit-identical restatement of the vendored smplx) on the host cores, bounded sample
-  torch_gpu_baseline : the same oracle ops on the B200 through stock PyTorch CUDA kernels (SURVEY.md 8(d) "composition" bar)
-`--impl reference` times that CPU path alone with the same JSON contract.
+Default workload = BASELINE.json configs[4] ("fit100k"): ONE 100 000-frame capture, 41 markers + 4 ghosts, noise,
+dropout, synthetic video-pose prior, video_mocap.yaml loss weights plus the trans_vel / temporal terms, cut into
+contiguous frame ranges over the N ranks (strong scaling; per iteration the ranks exchange the 1-/2-frame halo and one
+[d betas | loss] sum over NVLink peer memory).  One "step" = one fitting iteration over every frame = closure (SMPL
+forward, correspondence or marker loss, priors, temporal term, full backward) + fused Adam update; the K timed steps
+are ceil(K/2) chamfer-stage iterations followed by floor(K/2) marker-stage iterations (the two stages of the yaml).
+  value : parameters / markers / prior resident in HBM, C-ABI calls replayed from one CUDA graph per stage,
+          CUDA-event timed between barriers, max over ranks
+  e2e   : the reference's stage functions (optim_chamfer -> compute_nearest_points -> optim_markers) on pinned HOST
+          tensors: H2D of the capture, the same number of iterations, D2H of the fitted parameters, all inside the
+          timed region
+  roofline : dominant kernel of the step, timed live with CUDA events inside the library (a separate eager pass)
+  parity   : 64 sampled frames of the first closure evaluation checked against the CPU oracle (vertices, indices, grads)
+  cpu_baseline : the oracle closures + torch.optim.Adam on the host cores, bounded sample of the same capture
+`--impl reference` times that CPU path alone on the same config with the same JSON contract.
+`--workload lbs` is BASELINE.json configs[1] (lbs() forward+backward microbench, weak scaling).
 """
 from __future__ import annotations
 
@@ -145,7 +152,7 @@ def torch_gpu_oracle_rate(frames: int, reps: int, dev, seed: int):
     return frames / (ms * 1e-3), ms
 
 
-def run_reference(args, rank, world):
+def run_reference_lbs(args, rank, world):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
@@ -160,8 +167,10 @@ def run_reference(args, rank, world):
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD % args.frames, "frames_per_gpu": args.frames,
-                   "note": "reference smplx/PyTorch lbs() fwd+bwd on host cores (oracle port, bit-identical to the "
-                           "vendored smplx); each step is a %d-frame sample of the workload" % sample},
+                   "parallelism": "frame-range shards x%d" % world,
+                   "l2": "inputs larger than L2 (>= 680 MB streamed per step)"},
+        "note": "reference smplx/PyTorch lbs() fwd+bwd on host cores (oracle port, bit-identical to the vendored smplx); "
+                "each step runs %d frames" % sample,
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": "%d of %d frames per step, torch threads=%d" % (sample, args.frames, threads)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -171,7 +180,7 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
-# fitting-loop workloads (BASELINE.json configs[2] "fit5k", configs[3] "mht", configs[4] "fit100k")
+# fitting-loop workloads (BASELINE.json configs[4] "fit100k" = the default, configs[2] "fit5k", configs[3] "mht")
 # ------------------------------------------------------------------------------------------------
 FIT_TRAFFIC_KEYS = ("nn_argmin_presorted", "rows_forward", "rows_backward", "adam_step")
 FIT_WORKLOADS = {
@@ -180,44 +189,221 @@ FIT_WORKLOADS = {
               "synthetic video-pose prior", 5000, 1, "weak", False),
     "mht": ("configs[3]: mht_rotation.yaml, 64 yaw hypotheses x 2000 frames stacked along the frame axis and sharded by "
             "hypothesis", 2000, 64, "strong", False),
-    "fit100k": ("configs[4]: 100 000-frame capture sharded by frame range, trans_vel + temporal terms on "
-                "(1- and 2-frame halo by P2P send/recv)", 100000, 1, "strong", True),
+    "fit100k": ("configs[4]: 100k-frame long-capture marker fit sharded by frame range, trans_vel + temporal terms on "
+                "(1- and 2-frame halo at shard boundaries)", 100000, 1, "strong", True),
 }
+LOSS_CH = {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0}      # config/video_mocap.yaml:19-31
+LOSS_MK = {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0}             # config/video_mocap.yaml:41-50
 
 
-def run_fit(args, rank, world, local, dev):
-    """One step = one closure evaluation + fused Adam update over this rank's frames.  Steps alternate between the
-    two stages of the yaml in equal numbers: K chamfer-stage iterations (full lbs() forward -> correspondence ->
-    row-sparse backward -> priors -> Adam) then K marker-stage iterations (row-sparse forward/backward)."""
+def fit_losses(temporal):
+    lc, lm = dict(LOSS_CH), dict(LOSS_MK)
+    if temporal:
+        lc["trans_vel"] = 1.0
+        lm["temporal"] = 1.0
+    return lc, lm
+
+
+def fit_config(args, world):
+    """The `config` object of the JSON line: identical on the `ours` and `reference` arms (what differs between the
+    arms -- graph replay, the CPU arm's frame sample -- is reported outside it, in `run` / `cpu_baseline.sample`)."""
+    desc, Ftot, H, scaling, temporal = FIT_WORKLOADS[args.workload]
+    if args.frames:
+        Ftot = args.frames
+    lc, lm = fit_losses(temporal)
+    per = "per GPU" if scaling == "weak" else "in total"
+    return {"workload": desc, "name": args.workload, "frames": Ftot, "frames_are": per, "hypotheses": H,
+            "markers": 45 if args.workload != "mht" else 41,
+            "model": "synthetic SMPL-shaped (6890 vertices, 24 joints, 10 betas, 207 posedirs, top-4 skinning weights)",
+            "losses": {"chamfer": lc, "marker": lm}, "optimizer": "Adam lr 0.01 (fused on the GPU arm, torch.optim.Adam on "
+            "the CPU arm)", "step": "one fitting iteration over all frames (closure + Adam); K steps = ceil(K/2) "
+            "chamfer-stage + floor(K/2) marker-stage iterations", "parallelism": "frame-range shards x%d" % world,
+            "l2": "per-iteration working set (vertices of this rank's frames, >= 400 MB) exceeds L2: streamed through HBM"}
+
+
+def make_fit_capture(args, rank, world, model):
+    """-> (capture, lo, hi, frames_global, H): this rank's slice [lo, hi) of the synthetic capture."""
+    from uuo_mocap_b200 import synthetic
+    from uuo_mocap_b200.dist import frame_range
+    desc, Ftot, H, scaling, temporal = FIT_WORKLOADS[args.workload]
+    if args.frames:
+        Ftot = args.frames
+    n_ghost, drop = (0, 0.0) if args.workload == "mht" else (4, 0.05)
+    if scaling == "weak":            # independent sequences: no cross-rank term
+        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=3 + rank, n_ghost=n_ghost, dropout_p=drop,
+                                     noise_std=0.002)
+        return cap, 0, Ftot, Ftot * world, H
+    if H > 1:                        # hypotheses are independent; sharded by hypothesis
+        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=4, noise_std=0.002)
+        return cap, 0, Ftot, Ftot * H, H
+    cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=5, n_ghost=n_ghost, dropout_p=drop, noise_std=0.002)
+    lo, hi = frame_range(Ftot, rank, world)
+    return cap, lo, hi, Ftot, H
+
+
+def cpu_fit_steps(cap, model, frames, temporal, n_ch, n_mk, warm, device=None):
+    """Oracle chamfer / marker closures (forward + backward) + torch.optim.Adam on the first `frames` frames of the
+    capture, on the host cores (or, with `device`, the same torch ops through stock PyTorch CUDA kernels: the SURVEY.md
+    8(d) "composition" bar).  `warm` untimed iterations per stage, then n_ch + n_mk timed ones.
+    -> dict(seconds, chamfer_s, marker_s per iteration)."""
+    from oracle import closures
+    from oracle.smpl_oracle import OracleSMPL
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    orc = OracleSMPL.from_model(model)
+    on_gpu = device is not None
+    if on_gpu:
+        orc = orc.to(device)
+    sync = (lambda: torch.cuda.synchronize(device)) if on_gpu else (lambda: None)
+    frames = min(frames, cap.markers.shape[0])
+    sl = slice(0, frames)
+    where = device if on_gpu else "cpu"
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[sl])).to(where)
+    mk, opose, obetas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas).to(where)
+    root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
+    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, mk.shape[1]).astype(np.int64)).to(mk.device)
+    lc, lm = fit_losses(temporal)
+    res = {}
+    for stage, n in (("chamfer", n_ch), ("marker", n_mk)):
+        pose = opose.clone().requires_grad_(True)
+        betas = obetas.clone().requires_grad_(True)
+        tr = trans.clone().requires_grad_(True)
+        if stage == "chamfer":
+            z = torch.zeros(frames, 1, 1, device=mk.device, requires_grad=True)
+            params = [tr, z, betas, pose]
+            fn = lambda: closures.chamfer_stage_loss(orc, mk, pose, opose, betas, obetas, root, tr, z, lc)
+        else:
+            rt = root.clone().requires_grad_(True)
+            params = [pose, betas, rt, tr]
+            fn = lambda: closures.marker_stage_loss(orc, mk, pose, opose, betas, obetas, rt, tr, vidx, lm)
+        opt = torch.optim.Adam(params, lr=0.01)
+        ts = []
+        for i in range(warm + n):
+            sync()
+            t0 = time.perf_counter()
+            opt.zero_grad()
+            fn().backward()
+            opt.step()
+            sync()
+            if i >= warm:
+                ts.append(time.perf_counter() - t0)
+        res[stage + "_s"] = float(np.mean(ts)) if ts else 0.0
+        res[stage + "_total_s"] = float(np.sum(ts))
+    res["seconds"] = res["chamfer_total_s"] + res["marker_total_s"]
+    res["frames"] = frames
+    res["threads"] = threads
+    return res
+
+
+def run_reference_fit(args, rank, world):
+    """`--impl reference`: the reference's CPU implementation of the same fitting iteration (oracle port of
+    optimization.py:187-275 / :329-394 + torch.optim.Adam) on the host cores with all threads, same config; each step
+    runs on a bounded contiguous sample of the capture (the full 100 000 frames would take ~50 s per step)."""
+    if rank != 0:
+        return
+    import uuo_mocap_b200  # noqa: F401
+    from uuo_mocap_b200 import synthetic
+    desc, Ftot, H, scaling, temporal = FIT_WORKLOADS[args.workload]
+    model = synthetic.make_model("top4")
+    sample = args.ref_frames
+    n_ghost, drop = (0, 0.0) if args.workload == "mht" else (4, 0.05)
+    seed = {"fit5k": 3, "mht": 4, "fit100k": 5}[args.workload]
+    # a capture of `sample` frames from the same generator and seed (same statistics: motion bandwidth, noise, dropout,
+    # ghosts; the per-frame cost of the CPU path does not depend on which frames are drawn)
+    cap = synthetic.make_capture(model, sample, num_markers=41, seed=seed, n_ghost=n_ghost, dropout_p=drop, noise_std=0.002)
+    K = args.steps
+    n_ch, n_mk = (K + 1) // 2, K // 2
+    t0 = time.perf_counter()
+    r = cpu_fit_steps(cap, model, sample, temporal, n_ch, n_mk, max(1, args.warmup // 2))
+    wall = time.perf_counter() - t0
+    rate = sample * K / r["seconds"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": K,
+        "warmup": args.warmup, "ms_per_step": r["seconds"] / K * 1e3, "higher_is_better": True, "scaling": scaling,
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": fit_config(args, world),
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": r["threads"], "kind": "port",
+                         "sample": "each step = one iteration over a %d-frame contiguous sample of the capture "
+                                   "(chamfer %.3f s, marker %.3f s per iteration), torch threads=%d"
+                                   % (sample, r["chamfer_s"], r["marker_s"], r["threads"])},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": wall,
+        "note": "reference path on host cores: oracle port of the stage closures (vendored-smplx lbs + restated pytorch3d "
+                "chamfer) + torch.optim.Adam; the Python reference itself cannot be installed here (pytorch3d absent)",
+    }
+    _emit(line)
+
+
+def fit_parity_sample(prob, pb, root_d, cap, lo, model, n_sample=64, check=True):
+    """Self-check of the bench run: ONE chamfer-closure evaluation (full_chamfer term only, so the
+    per-frame gradients do not depend on the other frames) over all of this rank's frames on the CUDA path, then
+    `n_sample` frames spread over the range are checked against the CPU oracle run on just those frames:
+    vertices (1e-5 relative, per frame), correspondence indices (bit-exact on identical vertices), d loss / d pose,
+    d trans, d yaw (1e-4 relative).  Frames are independent in this term, so the sample is a fair check of the whole."""
+    from uuo_mocap_b200 import fit as fitm
+    from oracle import closures, p3d_oracle as p3d
+    from oracle.smpl_oracle import OracleSMPL
+    F = prob.F
+    pb.grad.zero_()
+    fitm.chamfer_closure(prob, pb, root_d, {"full_chamfer": 10.0})
+    torch.cuda.synchronize()
+    if not check:                       # the closure holds the shards' exchange: every rank runs it, rank 0 checks
+        return None
+    sel = np.unique(np.linspace(0, F - 1, n_sample).round().astype(np.int64))
+    st = torch.from_numpy(sel).to(prob.dev)
+    ids = prob.twin.visit_ids.long()                     # row r of the twin's vertex array = original vertex ids[r]
+    v_gpu = torch.empty((len(sel), prob.mh.V, 3), device=prob.dev)
+    v_gpu[:, ids] = prob.vertices[st]
+    v_gpu = v_gpu.cpu()
+    idx_gpu = prob.idx[st].cpu().long()
+    mask = prob.mask[st].cpu()
+    g_gpu = {k: pb.gviews[k][st].cpu().numpy() for k in ("pose_body", "trans", "z_angle")}
+    pose = pb.views["pose_body"][st].cpu().clone().requires_grad_(True)
+    trans = pb.views["trans"][st].cpu().clone().requires_grad_(True)
+    z = pb.views["z_angle"][st].cpu().clone().reshape(-1, 1, 1).requires_grad_(True)
+    betas = pb.views["betas"].cpu().clone().reshape(1, -1)
+    root = root_d[st].cpu()
+    mk = prob.markers[st].cpu()
+    orc = OracleSMPL.from_model(model)
+    torch.set_num_threads(os.cpu_count() or 1)
+    loss = closures.chamfer_stage_loss(orc, mk, pose, pose.detach(), betas, betas, root, trans, z, {"full_chamfer": 10.0})
+    loss.backward()
+    with torch.no_grad():
+        zr = p3d.compute_root_orient_z(z) @ root
+        v_ref = orc.smpl_inference(p3d.normalize_rot(pose), betas.repeat(len(sel), 1), p3d.normalize_rot(zr), trans)["vertices"]
+    per_frame = lambda a, b: float((np.abs(a - b).reshape(len(sel), -1).max(1)
+                                    / np.maximum(np.abs(b).reshape(len(sel), -1).max(1), 1e-30)).max())
+    v_err = per_frame(v_gpu.numpy(), v_ref.numpy())
+    _, idx_ref = p3d.knn_k1(mk, v_gpu)                   # the oracle's argmin on the SAME vertices: must agree exactly
+    on = mask != 0
+    idx_ok = bool(torch.equal(idx_gpu[on], idx_ref[on]))
+    # the oracle normalised by the sample's weight sum, the run by the global one
+    scale = float(mask.sum()) / prob.wsum_global
+    rel = lambda a, b: float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+    g_err = max(rel(g_gpu["pose_body"], pose.grad.numpy() * scale), rel(g_gpu["trans"], trans.grad.numpy() * scale),
+                rel(g_gpu["z_angle"], z.grad.numpy().reshape(-1) * scale))
+    return {"frames_checked": int(len(sel)), "of_frames": int(F), "vertices_rel_err_per_frame": v_err, "vertices_tol": 1e-5,
+            "idx_bit_exact": idx_ok, "markers_compared": int(on.sum()), "grad_rel_err": g_err, "grad_tol": 1e-4,
+            "ok": bool(v_err < 1e-5 and idx_ok and g_err < 1e-4),
+            "against": "oracle/ (CPU restatement pinned on the vendored smplx; pytorch3d ops restated)"}
+
+
+def run_fit(args, rank, world, local, dev, light=False):
+    """K steps = ceil(K/2) chamfer-stage iterations (full lbs() forward -> correspondence -> row-sparse backward ->
+    priors [-> trans_vel halo] -> shard sum -> Adam) then floor(K/2) marker-stage iterations (row-sparse forward /
+    backward [-> temporal halo] -> shard sum -> Adam) over this rank's frames.  `light`: device-timed numbers only
+    (used for the `other_workloads` entries of the default line), returns the dict instead of printing it."""
     import uuo_mocap_b200  # noqa: F401
     from uuo_mocap_b200 import synthetic, ops, fit as fitm
     from uuo_mocap_b200.dist import Shard, frame_range
     from uuo_mocap_b200.smpl import SMPL, _as_struct
 
-    desc, Ftot, H, scaling, temporal = FIT_WORKLOADS[args.workload]
-    if args.frames:
-        Ftot = args.frames
+    desc, _, _, scaling, temporal = FIT_WORKLOADS[args.workload]
     model = synthetic.make_model("top4")
     smpl = SMPL(_as_struct(model), device=dev)
-    shard = Shard.from_env() if world > 1 else Shard()
-    n_ghost, drop = (0, 0.0) if args.workload == "mht" else (4, 0.05)
-    if scaling == "weak":
-        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=3 + rank, n_ghost=n_ghost, dropout_p=drop,
-                                     noise_std=0.002)
-        lo, hi = 0, Ftot
-        shard_fit = Shard()                 # independent sequences: no cross-rank term
-        frames_global = Ftot * world
-    elif H > 1:
-        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=4, noise_std=0.002)
-        lo, hi = 0, Ftot
-        shard_fit = Shard()                 # hypotheses are independent; sharded by hypothesis below
-        frames_global = Ftot * H
-    else:
-        cap = synthetic.make_capture(model, Ftot, num_markers=41, seed=5, n_ghost=n_ghost, dropout_p=drop,
-                                     noise_std=0.002)
-        lo, hi = frame_range(Ftot, rank, world)
-        shard_fit = shard
-        frames_global = Ftot
+    cap, lo, hi, frames_global, H = make_fit_capture(args, rank, world, model)
+    Ftot = cap.markers.shape[0]
+    sharded = scaling == "strong" and H == 1 and world > 1
+    shard_fit = Shard.from_env(peer_device=dev) if sharded else Shard()
     T = lambda a: torch.from_numpy(np.ascontiguousarray(a[lo:hi]))
     markers, o_pose, o_betas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas)
     root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
@@ -231,25 +417,25 @@ def run_fit(args, rank, world, local, dev):
         groups = Hl
     else:
         groups = 1
-    F = markers.shape[0]
-    M = markers.shape[1]
+    F, M = markers.shape[0], markers.shape[1]
     prob = fitm.FitProblem(smpl, markers, o_pose, o_betas, shard_fit, groups)
     betas0 = o_betas.reshape(1, -1).repeat(groups, 1)
     pb_ch = fitm.ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F), "betas": betas0, "pose_body": o_pose}, dev)
     pb_mk = fitm.ParamBlock.build({"pose_body": o_pose, "betas": betas0, "root_orient": root, "trans": trans}, dev)
     root_d = root.to(dev).contiguous()
-    loss_ch = {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0}
-    loss_mk = {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0}
-    if temporal:
-        loss_ch["trans_vel"] = 1.0
-        loss_mk["temporal"] = 1.0
+    loss_ch, loss_mk = fit_losses(temporal)
     vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, M).astype(np.int32)).to(dev)
     if groups > 1:  # every hypothesis carries its own correspondences (fit.fit_hypotheses): indices [groups, M]
         vidx = vidx.reshape(1, M).expand(groups, M).contiguous()
     state = {k: (torch.zeros_like(pb.flat), torch.zeros_like(pb.flat)) for k, pb in (("ch", pb_ch), ("mk", pb_mk))}
     counters = {k: torch.zeros(1, dtype=torch.int32, device=dev) for k in ("ch", "mk")}
     graphs = {}
-    use_graph = world == 1 and not args.no_graph        # the multi-rank closures call NCCL from Python: left eager
+    use_graph = shard_fit.graph_safe and not args.no_graph
+
+    parity = None
+    if not light and not args.no_parity:
+        parity = fit_parity_sample(prob, pb_ch, root_d, cap, lo, model, check=rank == 0)   # every rank runs the closure
+        prob.pos.fill_(-1)
 
     def step(stage):
         pb = pb_ch if stage == "ch" else pb_mk
@@ -264,59 +450,74 @@ def run_fit(args, rank, world, local, dev):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(stage, n, profile=False):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        if profile:
-            ops.profile_enable(True)
-        if not profile and use_graph and stage not in graphs:   # one iteration captured once, replayed n times
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                step(stage)
-            graphs[stage] = g
-            g.replay()
-            barrier()
-        e0.record()
+    def run_n(stage, n, replay):
         for _ in range(n):
-            if not profile and use_graph:
+            if replay:
                 graphs[stage].replay()
             else:
                 step(stage)
-        e1.record()
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
-        prof = None
-        if profile:
-            prof = ops.profile_read()
-            ops.profile_enable(False)
-        own = float(t.item())
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), own, prof
 
+    K = args.steps
+    n_ch, n_mk = (K + 1) // 2, K // 2
     for stage in ("ch", "mk"):
         for _ in range(args.warmup):
             step(stage)
-    K = args.steps
+    barrier()
     sampler = ClockSampler(local) if rank == 0 else None
-    # pass 1 (eager, per-kernel events on): the kernel breakdown behind `roofline`; pass 2 (timed): the same K
-    # iterations as CUDA-graph replays on one GPU, eager under torchrun
-    _, own_ch, prof_ch = timed("ch", K, profile=True)
-    _, own_mk, prof_mk = timed("mk", K, profile=True)
-    ms_ch, _, _ = timed("ch", K)
-    ms_mk, _, _ = timed("mk", K)
-    value = frames_global * 2 * K / ((ms_ch + ms_mk) * 1e-3)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    # ---- pass 1 (eager, the library's per-kernel events on): the kernel breakdown behind `roofline`
+    ops.profile_enable(True)
+    p0, p1, p2 = ev(), ev(), ev()
+    barrier()
+    p0.record(); run_n("ch", n_ch, False); p1.record(); run_n("mk", n_mk, False); p2.record()
+    barrier()
+    prof = ops.profile_read()
+    ops.profile_enable(False)
+    prof_ms = p0.elapsed_time(p2)
+
+    # ---- pass 2 (the timed K steps): one captured iteration per stage replayed (eager when graphs are off)
+    if use_graph:
+        for stage in ("ch", "mk"):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, capture_error_mode="thread_local" if world > 1 else "global"):
+                step(stage)
+            graphs[stage] = g
+        run_n("ch", 1, True); run_n("mk", 1, True)
+    e0, e1, e2 = ev(), ev(), ev()
+    barrier()
+    e0.record(); run_n("ch", n_ch, use_graph); e1.record(); run_n("mk", n_mk, use_graph); e2.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e2), e0.elapsed_time(e1), e1.elapsed_time(e2)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_all, ms_ch, ms_mk = (float(x) for x in t.tolist())
+    value = frames_global * K / (ms_all * 1e-3)
+
+    def stage_rates():
+        return {"chamfer": {"iters": n_ch, "ms_per_iter": ms_ch / max(n_ch, 1),
+                            "frame_iters_per_sec": frames_global * n_ch / (ms_ch * 1e-3) if n_ch else None},
+                "marker": {"iters": n_mk, "ms_per_iter": ms_mk / max(n_mk, 1),
+                           "frame_iters_per_sec": frames_global * n_mk / (ms_mk * 1e-3) if n_mk else None}}
+
+    kern = {k: round(v[0] / max(v[1], 1), 4) for k, v in (prof or {}).items()}
+    if light:
+        if sampler:
+            sampler.stop()
+        return {"value": value, "unit": UNIT, "ms_per_step": ms_all / K, "steps": K, "frames_this_rank": F,
+                "stages": stage_rates(), "ms_per_launch": kern, "cuda_graph": bool(use_graph)}
 
     # ---- e2e: the reference's stage functions with HOST tensors in and out (optim_chamfer -> compute_nearest_points
-    # -> optim_markers), K Adam iterations per stage, copies inside the timed region
-    cfg = fitm.default_config(num_iters=K, optimizer="adam", lr=0.01)
-    if temporal:
-        cfg["stages"]["chamfer"]["losses"]["trans_vel"] = 1.0
-        cfg["stages"]["marker"]["losses"]["temporal"] = 1.0
-    pin = lambda t: t.clone().pin_memory()
+    # -> optim_markers), the same n_ch / n_mk Adam iterations, copies inside the timed region
+    cfg = fitm.default_config(num_iters=n_ch, optimizer="adam", lr=0.01)
+    cfg["stages"]["marker"]["num_iters"] = n_mk
+    cfg["stages"]["chamfer"]["losses"], cfg["stages"]["marker"]["losses"] = dict(loss_ch), dict(loss_mk)
+    pin = lambda x: x.clone().pin_memory()
     h = {"markers": pin(markers), "pose": pin(o_pose), "root": pin(root), "trans": pin(trans), "betas": pin(betas0)}
-    h2d = sum(t.numel() * 4 for t in h.values()) + h["pose"].numel() * 4
+    h2d = sum(x.numel() * 4 for x in h.values()) + h["pose"].numel() * 4
     d2h = sum(h[k].numel() * 4 for k in ("pose", "root", "trans", "betas"))
+    del prob, pb_ch, pb_mk, state, graphs
+    torch.cuda.empty_cache()
 
     def e2e_once():
         mk = h["markers"].to(dev, non_blocking=True)
@@ -329,7 +530,7 @@ def run_fit(args, rank, world, local, dev):
         else:
             vi = vidx
         fitm.optim_markers(mk, pose, opose, bt, o_betas, rt, tr, vi, None, smpl, cfg, problem=p, groups=groups)
-        return [t.to("cpu", non_blocking=False) for t in (pose, rt, tr, bt)]
+        return [x.to("cpu", non_blocking=False) for x in (pose, rt, tr, bt)]
 
     e2e_once()
     barrier()
@@ -339,12 +540,15 @@ def run_fit(args, rank, world, local, dev):
     t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = frames_global * 2 * K / float(t.item())
+    e2e_s = float(t.item())
+    e2e_value = frames_global * K / e2e_s
     clocks = sampler.stop() if sampler else None
 
+    line = None
     if rank == 0:
         peaks = _peaks()
         Vn = V
+        nflat = F * 211 + 10 * groups
         algo = {   # algorithmic bytes (or flops) per launch over this rank's F frames
             "vposed_gemm": ("tensor", 2.0 * F * KC * 3 * Vn),
             "skin_forward": ("hbm", F * (2 * 3 * Vn * 4 + J * 48 + 12)),
@@ -355,114 +559,62 @@ def run_fit(args, rank, world, local, dev):
             "rows_backward": ("hbm", F * (KC * 4 + J * 48 + M * 12 + 292 * 4 + 224 * 4)),
             "fk_forward": ("hbm", F * (916 + KC * 4 + J * 48 + J * 12)),
             "fk_backward": ("hbm", F * (2 * 916 + 292 * 4 + 224 * 4)),
-            "adam_step": ("hbm", pb_ch.flat.numel() * 4 * 7),
+            "adam_step": ("hbm", nflat * 4 * 7),
         }
         tp = os.path.join(ROOT, "profiles", "traffic.json")       # ncu DRAM bytes per launch, captured at F = 5000
         traffic = json.load(open(tp)) if os.path.exists(tp) else {}
-
-        def dominant(prof, ms):
-            if not prof:
-                return None
+        roofline = None
+        if prof:
             dom = max(prof.items(), key=lambda kv: kv[1][0])[0]
-            kern = {k: round(v[0] / max(v[1], 1), 4) for k, v in prof.items()}
-            out = {"kernel": dom, "share_of_stage": prof[dom][0] / ms, "ms_per_launch": kern}
-            if dom in algo:
-                bound, work = algo[dom]
-                dur = prof[dom][0] / max(prof[dom][1], 1) * 1e-3
-                if bound == "hbm":
-                    ach, peak, unit = work / dur / 1e9, peaks["hbm"], "GB/s"
-                else:
-                    ach, peak, unit = work / dur / 1e12, peaks["bf16"] / 2.0, "TFLOP/s"
-                out.update({"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak,
-                            "peak_source": peaks["src"],
-                            # ncu captures of the fit kernels were taken at F = 5000 (the lbs kernels at F = 4096)
-                            "traffic": traffic.get(dom) if F == 5000 and dom in FIT_TRAFFIC_KEYS else None})
-            return out
-        r_ch, r_mk = dominant(prof_ch, own_ch), dominant(prof_mk, own_mk)
-        roofline = dict(r_ch or {})
-        roofline.setdefault("traffic", None)
-        roofline["marker_stage"] = r_mk
+            roofline = {"kernel": dom, "share_of_step": prof[dom][0] / prof_ms, "launches": prof[dom][1],
+                        "ms_per_launch": kern, "traffic": None}
+            table = {}
+            for k, (bound, work) in algo.items():
+                if k in prof and prof[k][1] > 0:
+                    dur = prof[k][0] / prof[k][1] * 1e-3
+                    if bound == "hbm":
+                        ach, peak, unit = work / dur / 1e9, peaks["hbm"], "GB/s"
+                    else:
+                        ach, peak, unit = work / dur / 1e12, peaks["bf16"] / 2.0, "TFLOP/s"
+                    table[k] = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak}
+            if dom in table:
+                roofline.update(table[dom])
+                roofline["peak_source"] = peaks["src"] + (" (TF32 dense = bf16/2; logical flops, the 3xTF32 split issues 3x)"
+                                                          if table[dom]["bound"] == "tensor" else "")
+                # ncu captures of the fit kernels were taken at F = 5000 per launch
+                roofline["traffic"] = traffic.get(dom) if F == 5000 and dom in FIT_TRAFFIC_KEYS else None
+            roofline["per_kernel"] = table
         cpu = tg = None
         if world == 1 and not args.no_cpu_baseline:
-            cpu = cpu_closure_rate(args.ref_frames, cap, model)
+            r = cpu_fit_steps(cap, model, args.ref_frames, temporal, 2, 2, 1)
+            cpu = {"value": r["frames"] * 4 / r["seconds"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+                   "sample": "first %d frames of the capture, 2 chamfer + 2 marker iterations (closure fwd+bwd + torch Adam) "
+                             "after 1 warm-up each, torch threads=%d" % (r["frames"], r["threads"]),
+                   "chamfer_s": r["chamfer_s"], "marker_s": r["marker_s"]}
             try:                              # a reported bar, never a reason to lose the bench line
                 torch.cuda.empty_cache()
-                tg = cpu_closure_rate(min(F, 2048), cap, model, device=dev)
+                r = cpu_fit_steps(cap, model, 2048, temporal, 2, 2, 1, device=dev)
+                tg = {"value": r["frames"] * 4 / r["seconds"], "unit": UNIT, "frames": r["frames"],
+                      "kind": "oracle chamfer + marker closures (fwd+bwd) + torch Adam through stock PyTorch CUDA ops (fp32, TF32 "
+                              "off), frame chunks of 256", "chamfer_s": r["chamfer_s"], "marker_s": r["marker_s"]}
             except Exception as e:
                 tg = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:160])}
+        launches = int(sum(v[1] for v in (prof or {}).values()))
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": 2 * K, "warmup": args.warmup,
-            "ms_per_step": (ms_ch + ms_mk) / (2 * K), "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "frames_this_rank": F, "frames_global": frames_global, "markers": M,
-                       "hypotheses": H, "parallelism": "frame-range shards x%d" % world, "optimizer": "fused Adam", "cuda_graph": bool(use_graph),
-                       "l2": "per-iteration working set >= %d MB (vertices) streamed through HBM" % (F * V * 12 // 2**20)},
-            "stages": {"chamfer": {"ms_per_iter": ms_ch / K, "frame_iters_per_sec": frames_global * K / (ms_ch * 1e-3)},
-                       "marker": {"ms_per_iter": ms_mk / K, "frame_iters_per_sec": frames_global * K / (ms_mk * 1e-3)}},
-            "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // (2 * K), "d2h_bytes_per_step": d2h // (2 * K),
-                    "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d Adam iterations "
-                            "per stage, one H2D of the capture and one D2H of the fitted parameters per call" % K},
-            "gpu_launches": int(sum(v[1] for v in (prof_ch or {}).values()) + sum(v[1] for v in (prof_mk or {}).values())),
-            "roofline": roofline, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "ms_per_step": ms_all / K, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": fit_config(args, world),
+            "run": {"frames_this_rank": F, "frames_global": frames_global, "cuda_graph": bool(use_graph),
+                    "exchange": ("peer-memory kernels (uuo_comm_*)" if shard_fit.comm is not None else
+                                 ("torch.distributed" if shard_fit.world > 1 else "none (one shard)"))},
+            "stages": stage_rates(), "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
+                    "seconds": e2e_s,
+                    "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d + %d Adam "
+                            "iterations, one H2D of this rank's capture and one D2H of its fitted parameters per call" % (n_ch, n_mk)},
+            "gpu_launches": launches, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
         }
-        _emit(line)
-    if world > 1:
-        dist.destroy_process_group()
-
-
-def cpu_closure_rate(frames, cap, model, device=None):
-    """Oracle chamfer + marker closures (fwd + bwd) + torch Adam on the host cores, `frames` frames.
-    With ``device``: the same torch ops on that CUDA device through stock PyTorch kernels (the SURVEY.md 8(d)
-    "composition" bar of the fitting loop), timed with a synchronize on both sides of every iteration."""
-    from oracle import closures
-    from oracle.smpl_oracle import OracleSMPL
-    threads = os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    orc = OracleSMPL.from_model(model)
-    on_gpu = device is not None
-    if on_gpu:
-        orc = orc.to(device)
-    sync = (lambda: torch.cuda.synchronize(device)) if on_gpu else (lambda: None)
-    sl = slice(0, frames)
-    T = lambda a: torch.from_numpy(np.ascontiguousarray(a[sl])).to(device if on_gpu else "cpu")
-    mk, opose, obetas = T(cap.markers), T(cap.prior_pose_body), torch.from_numpy(cap.prior_betas).to(device if on_gpu else "cpu")
-    root, trans = T(cap.prior_root_orient), T(cap.prior_trans)
-    vidx = torch.from_numpy(np.resize(cap.marker_vertex_ids, mk.shape[1]).astype(np.int64)).to(mk.device)
-    res = {}
-    for stage in ("chamfer", "marker"):
-        pose = opose.clone().requires_grad_(True)
-        betas = obetas.clone().requires_grad_(True)
-        tr = trans.clone().requires_grad_(True)
-        if stage == "chamfer":
-            z = torch.zeros(frames, 1, 1, device=mk.device, requires_grad=True)
-            params = [tr, z, betas, pose]
-            fn = lambda: closures.chamfer_stage_loss(orc, mk, pose, opose, betas, obetas, root, tr, z,
-                                                     {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0})
-        else:
-            rt = root.clone().requires_grad_(True)
-            params = [pose, betas, rt, tr]
-            fn = lambda: closures.marker_stage_loss(orc, mk, pose, opose, betas, obetas, rt, tr, vidx,
-                                                    {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0})
-        opt = torch.optim.Adam(params, lr=0.01)
-        ts = []
-        for i in range(3):
-            sync()
-            t0 = time.perf_counter()
-            opt.zero_grad()
-            fn().backward()
-            opt.step()
-            sync()
-            ts.append(time.perf_counter() - t0)
-        res[stage + "_s"] = float(np.median(ts[1:]))
-    if on_gpu:
-        return {"value": 2 * frames / (res["chamfer_s"] + res["marker_s"]), "unit": UNIT, "frames": frames,
-                "kind": "oracle chamfer + marker closures (fwd+bwd) + torch Adam through stock PyTorch CUDA ops (fp32, TF32 off), "
-                        "frame chunks of 256, median of 2 after 1 warm-up", "chamfer_s": res["chamfer_s"], "marker_s": res["marker_s"]}
-    return {"value": 2 * frames / (res["chamfer_s"] + res["marker_s"]), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": "%d frames, chamfer + marker closure (fwd+bwd) + Adam, median of 2 after 1 warm-up, torch threads=%d"
-                      % (frames, threads),
-            "chamfer_s": res["chamfer_s"], "marker_s": res["marker_s"]}
+    return line
 
 
 WORKLOAD = "configs[1]: SMPL lbs() forward+backward microbench, %d frames per GPU, synthetic SMPL-shaped model (dense-24 weights)"
@@ -471,13 +623,16 @@ WORKLOAD = "configs[1]: SMPL lbs() forward+backward microbench, %d frames per GP
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--frames", type=int, default=0, help="frames per GPU (lbs: default 4096; fit workloads: their own)")
-    ap.add_argument("--workload", default="lbs", choices=["lbs"] + sorted(FIT_WORKLOADS))
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--frames", type=int, default=0, help="frames (lbs: per GPU, default 4096; fit workloads: their own)")
+    ap.add_argument("--workload", default="fit100k", choices=["lbs"] + sorted(FIT_WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ref-frames", type=int, default=256)
+    ap.add_argument("--ref-frames", type=int, default=0,
+                    help="frames per step of the CPU arm (default: 1024 for the fit workloads, all 4096 for lbs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="fit workloads: skip the oracle self-check of the first closure")
+    ap.add_argument("--no-extras", action="store_true", help="skip the short runs of the other workloads (N = 1 only)")
     ap.add_argument("--e2e-sync", action="store_true", help="lbs e2e: one synchronous call per step instead of the double-buffered loop")
     ap.add_argument("--no-graph", action="store_true", help="fit workloads: time eager launches instead of graph replays")
     args = ap.parse_args()
@@ -487,9 +642,15 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        args.frames = args.frames or 4096
-        run_reference(args, rank, world)
+        if args.workload == "lbs":
+            args.frames = args.frames or 4096
+            args.ref_frames = args.ref_frames or args.frames      # every step runs ALL the frames of the config
+            run_reference_lbs(args, rank, world)
+        else:
+            args.ref_frames = args.ref_frames or 1024
+            run_reference_fit(args, rank, world)
         return
+    args.ref_frames = args.ref_frames or (256 if args.workload == "lbs" else 1024)
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl=ours) needs a CUDA device: the product path has no CPU fallback")
@@ -499,13 +660,33 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    if args.workload != "lbs":
-        if args.steps == 200:
-            args.steps = 50
-        run_fit(args, rank, world, local, dev)
-        return
-    args.frames = args.frames or 4096
+    if args.workload == "lbs":
+        line = run_lbs(args, rank, world, local, dev)
+    else:
+        line = run_fit(args, rank, world, local, dev)
+        if rank == 0 and world == 1 and not args.no_extras:
+            # the other configs of BASELINE.json, short device-timed runs carried as extra keys of the same line
+            import copy
+            other = {}
+            for name, steps in (("fit5k", 20), ("lbs", 20)):
+                a2 = copy.copy(args)
+                a2.workload, a2.steps, a2.frames, a2.warmup = name, steps, 0, 3
+                try:
+                    torch.cuda.empty_cache()
+                    other[name] = (run_lbs if name == "lbs" else run_fit)(a2, rank, world, local, dev, light=True)
+                except Exception as e:       # never a reason to lose the headline line
+                    other[name] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:160])}
+            line["other_workloads"] = other
+    if rank == 0 and line is not None:
+        _emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
+
+def run_lbs(args, rank, world, local, dev, light=False):
+    """BASELINE.json configs[1]: lbs() forward + backward over F frames per GPU (weak scaling, no data-path collective)."""
+    args.frames = args.frames or 4096
     import uuo_mocap_b200  # noqa: F401
     from uuo_mocap_b200 import synthetic, ops, _lib
     from uuo_mocap_b200._lib import check, ptr, stream_ptr
@@ -551,14 +732,27 @@ def main():
         step_device()
     e1.record()
     barrier()
-    ms = e0.elapsed_time(e1)
+    ms = e0.elapsed_time(e1)                          # pass 1: per-kernel events on (feeds roofline.ms_per_launch)
     prof = ops.profile_read()
     ops.profile_enable(False)
-    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):                       # pass 2: the timed K steps, events off
+        step_device()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
     value = F * world * args.steps / (ms_max * 1e-3)
+    if light:
+        if sampler:
+            sampler.stop()
+        return {"value": value, "unit": UNIT, "ms_per_step": ms_max / args.steps, "steps": args.steps, "frames_per_gpu": F,
+                "ms_per_launch": {k: round(v[0] / max(v[1], 1), 4) for k, v in prof.items()},
+                "step_hbm_roofline_frac": (168272.0 * F * args.steps / (ms_max * 1e-3) / 1e9) / _peaks()["hbm"],
+                "workload": WORKLOAD % F}
 
     # ---- e2e through the public API with host buffers ----
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
@@ -679,7 +873,7 @@ def main():
                         "traffic": traffic, "peak_source": peaks["src"] + (" (TF32 dense = bf16/2)" if bound == "tensor" else ""),
                         "share_of_step": prof[dom][0] / ms, "ms_per_launch": kernels}
         # whole-step HBM roofline: 168 272 algorithmic bytes per frame-iteration
-        step_frac = (168272.0 * F * args.steps / (ms * 1e-3) / 1e9) / peaks["hbm"]
+        step_frac = (168272.0 * F * args.steps / (ms_max * 1e-3) / 1e9) / peaks["hbm"]
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
@@ -707,12 +901,12 @@ def main():
                                       "double-buffered: copies of step i+1 (in) / i-1 (out) on a copy stream under the kernels of step i"},
             "gpu_launches": launches_per_step * args.steps, "roofline": roofline,
             "step_hbm_roofline_frac": step_frac, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
-            "note": "value: direct C-ABI calls with the library's per-kernel CUDA events ON over the timed region (they "
-                    "feed roofline.ms_per_launch; ~1-2 % overhead); e2e: SMPL.forward + autograd, events off",
+            "note": "value: direct C-ABI calls, events off; roofline.ms_per_launch from a separate pass of the same K steps with "
+                    "the library's per-kernel CUDA events on; e2e: SMPL.forward + autograd (parameters in, parameter "
+                    "gradients + a scalar out; vertices / joints stay on the device, they feed the backward)",
         }
-        _emit(line)
-    if world > 1:
-        dist.destroy_process_group()
+        return line
+    return None
 
 
 if __name__ == "__main__":
