@@ -206,6 +206,7 @@ int uuo_transvel_accumulate(const float* trans, const float* mm, const float* pr
  *                            neighbour's first n rows (n*D <= 1024); prev / next untouched at the ends of the sequence */
 typedef struct uuo_comm uuo_comm;
 int uuo_comm_create(int rank, int world, int device, uuo_comm** out);
+int uuo_comm_set_timeout(uuo_comm* c, double seconds);   /* a wait on a peer longer than this traps (default 60 s) */
 int uuo_comm_handle_bytes(void);
 int uuo_comm_export(uuo_comm* c, void* handle_host);
 int uuo_comm_connect(uuo_comm* c, const void* handles_host);

@@ -44,7 +44,7 @@ def test_fit_capture_end_to_end(get_model, tmp_path, with_root):
     assert out["pose_body"].shape == (F, 23, 3, 3) and out["betas"].shape == (F, 10)
     assert out["markers_labels"].shape == (F, mk.shape[1]) and len(out["scores"]) == 2
     assert out["mocap_markers"].shape == tuple(mk.shape) and out["mocap_frame_rate"] == 100.0
-    want = {"marker", "marker_final"} | ({"root"} if with_root else set())
+    want = {"chamfer", "marker", "marker_final"} | ({"root"} if with_root else set())      # test/test.py:131-143
     assert set(out["stages"]) == want
     R = out["pose_body"].reshape(-1, 3, 3)
     assert torch.allclose(R @ R.transpose(1, 2), torch.eye(3).expand_as(R), atol=1e-5)

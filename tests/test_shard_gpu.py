@@ -93,7 +93,7 @@ def test_transvel_kernel_halo_rows(world):
 
 def _local_shards(world, dev="cuda:0"):
     from uuo_mocap_b200.dist import PeerComm, Shard
-    comms = [PeerComm(r, world, dev) for r in range(world)]
+    comms = [PeerComm(r, world, dev, timeout_s=10.0) for r in range(world)]
     PeerComm.connect_local(comms)
     return [Shard(r, world, None, comms[r]) for r in range(world)], comms
 

@@ -51,6 +51,7 @@ SIGNATURES = {
     "uuo_profile_enable": (_I, [_I]),
     "uuo_profile_read": (_I, [_I, C.c_char_p, _I, C.POINTER(_F), C.POINTER(_I)]),
     "uuo_comm_create": (_I, [_I, _I, _I, C.POINTER(_P)]),
+    "uuo_comm_set_timeout": (_I, [_P, C.c_double]),
     "uuo_comm_handle_bytes": (_I, []),
     "uuo_comm_export": (_I, [_P, _P]),
     "uuo_comm_connect": (_I, [_P, _P]),

@@ -10,13 +10,14 @@
 // Slots are double-buffered by epoch parity: a rank can only be one epoch ahead of a peer it exchanges with,
 // because passing epoch e needs that peer's flag for e, which the peer writes after it finished reading e-1.
 // The epoch counters live in device memory, so a replayed graph advances them like eager launches do.
-// All ranks must issue the same sequence of comm calls.  A wait that lasts longer than UUO_COMM_TIMEOUT_NS traps.
+// All ranks must issue the same sequence of comm calls.  A wait that lasts longer than the communicator's time limit
+// (60 s unless uuo_comm_set_timeout says otherwise) traps instead of hanging the GPU.
 #include "common.cuh"
 
 #define UUO_COMM_MAXW 16
 #define UUO_COMM_MAXRED 1024
 #define UUO_COMM_MAXHALO 1024
-#define UUO_COMM_TIMEOUT_NS 60000000000ull
+#define UUO_COMM_TIMEOUT_NS 60000000000ull   // default; uuo_comm_set_timeout changes it per communicator
 
 struct Mailbox {
   uint32_t ar_flag[2][UUO_COMM_MAXW];
@@ -34,6 +35,7 @@ struct uuo_comm {
   PeerTable peers;
   bool opened[UUO_COMM_MAXW];   // mapped through IPC (to be closed)
   bool connected;
+  unsigned long long timeout_ns;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -49,11 +51,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t e) {
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t e, unsigned long long timeout_ns) {
   const unsigned long long t0 = globaltimer_ns();
   while ((int32_t)(ld_acquire_sys(p) - e) < 0) {
     __nanosleep(64);
-    if (globaltimer_ns() - t0 > UUO_COMM_TIMEOUT_NS) {
+    if (globaltimer_ns() - t0 > timeout_ns) {
       printf("uuo_comm: a peer did not arrive at epoch %u within the time limit\n", e);
       __trap();
     }
@@ -62,7 +64,8 @@ __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t e) {
 
 // x[n] <- sum over ranks of x[n], summed in rank order on every rank (identical bits everywhere)
 __global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
-                                                              float* __restrict__ x, int n) {
+                                                              float* __restrict__ x, int n,
+                                                              unsigned long long timeout_ns) {
   const uint32_t e = mine->ar_epoch + 1;
   const int par = e & 1;
   for (int p = 0; p < world; ++p) {
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, M
   __syncthreads();
   if (threadIdx.x < world) {
     st_release_sys(&peers.p[threadIdx.x]->ar_flag[par][rank], e);
-    wait_flag(&mine->ar_flag[par][threadIdx.x], e);
+    wait_flag(&mine->ar_flag[par][threadIdx.x], e, timeout_ns);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -89,7 +92,7 @@ __global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, M
 __global__ void __launch_bounds__(256) comm_halo_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
                                                         const float* __restrict__ x, int F, int D, int n,
                                                         float* __restrict__ prev, float* __restrict__ next, int ld,
-                                                        int col) {
+                                                        int col, unsigned long long timeout_ns) {
   const uint32_t e = mine->halo_epoch + 1;
   const int par = e & 1;
   const int cnt = n * D;
@@ -107,11 +110,11 @@ __global__ void __launch_bounds__(256) comm_halo_kernel(PeerTable peers, Mailbox
   __syncthreads();
   if (threadIdx.x == 0 && has_l) {
     st_release_sys(&peers.p[rank - 1]->halo_flag[par][1], e);
-    wait_flag(&mine->halo_flag[par][0], e);
+    wait_flag(&mine->halo_flag[par][0], e, timeout_ns);
   }
   if (threadIdx.x == 32 && has_r) {
     st_release_sys(&peers.p[rank + 1]->halo_flag[par][0], e);
-    wait_flag(&mine->halo_flag[par][1], e);
+    wait_flag(&mine->halo_flag[par][1], e, timeout_ns);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
@@ -131,6 +134,12 @@ extern "C" int uuo_comm_create(int rank, int world, int device, uuo_comm** out) 
   UUO_CUDA(cudaSetDevice(device));
   uuo_comm* c = new uuo_comm();
   c->rank = rank; c->world = world; c->device = device; c->connected = false;
+  c->timeout_ns = UUO_COMM_TIMEOUT_NS;
+  // load both kernels NOW: with lazy module loading the first launch of a kernel may have to wait for running kernels
+  // to finish, and a running exchange kernel waits for its peers
+  cudaFuncAttributes fa;
+  UUO_CUDA(cudaFuncGetAttributes(&fa, comm_all_reduce_kernel));
+  UUO_CUDA(cudaFuncGetAttributes(&fa, comm_halo_kernel));
   for (int i = 0; i < UUO_COMM_MAXW; ++i) { c->peers.p[i] = nullptr; c->opened[i] = false; }
   if (cudaMalloc(&c->mine, sizeof(Mailbox)) != cudaSuccess) {
     delete c;
@@ -144,6 +153,12 @@ extern "C" int uuo_comm_create(int rank, int world, int device, uuo_comm** out) 
   if (world == 1) c->connected = true;
   UUO_CUDA(cudaSetDevice(prev_dev));
   *out = c;
+  return UUO_OK;
+}
+
+extern "C" int uuo_comm_set_timeout(uuo_comm* c, double seconds) {
+  UUO_CHECK_ARG(c && seconds > 0.0 && seconds < 86400.0, "bad arguments");
+  c->timeout_ns = (unsigned long long)(seconds * 1e9);
   return UUO_OK;
 }
 
@@ -215,7 +230,8 @@ extern "C" int uuo_comm_all_reduce_sum(uuo_comm* c, float* x, int n, void* strea
   UUO_CHECK_ARG(n >= 0 && n <= UUO_COMM_MAXRED, "n must be <= 1024 floats");
   if (c->world == 1 || n == 0) return UUO_OK;
   ProfScope ps_("comm_all_reduce", (cudaStream_t)stream);
-  comm_all_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(c->peers, c->mine, c->rank, c->world, x, n);
+  comm_all_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(c->peers, c->mine, c->rank, c->world, x, n,
+                                                                      c->timeout_ns);
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
@@ -231,7 +247,7 @@ extern "C" int uuo_comm_halo_exchange(uuo_comm* c, const float* x, int F, int D,
   if (c->world == 1) return UUO_OK;
   ProfScope ps_("comm_halo", (cudaStream_t)stream);
   comm_halo_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(c->peers, c->mine, c->rank, c->world, x, F, D, n, prev, next,
-                                                        ld, col);
+                                                        ld, col, c->timeout_ns);
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }

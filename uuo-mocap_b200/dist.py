@@ -29,7 +29,7 @@ class PeerComm:
     """One rank's mailbox of the peer-memory transport (uuo_comm_*).  ``connect()`` trades the CUDA IPC handles
     through torch.distributed; ``connect_local`` links communicators created in one process (tests)."""
 
-    def __init__(self, rank: int, world: int, device):
+    def __init__(self, rank: int, world: int, device, timeout_s: Optional[float] = None):
         import ctypes as C
         from . import _lib
         self._lib = _lib
@@ -38,6 +38,8 @@ class PeerComm:
         h = C.c_void_p()
         _lib.check(_lib.lib().uuo_comm_create(self.rank, self.world, self.device.index or 0, C.byref(h)))
         self.handle = h
+        if timeout_s is not None:
+            _lib.check(_lib.lib().uuo_comm_set_timeout(h, float(timeout_s)))
 
     def connect(self, group=None) -> "PeerComm":
         import ctypes as C
