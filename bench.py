@@ -516,6 +516,7 @@ def run_fit(args, rank, world, local, dev, light=False):
     h = {"markers": pin(markers), "pose": pin(o_pose), "root": pin(root), "trans": pin(trans), "betas": pin(betas0)}
     h2d = sum(x.numel() * 4 for x in h.values()) + h["pose"].numel() * 4
     d2h = sum(h[k].numel() * 4 for k in ("pose", "root", "trans", "betas"))
+    h_out = {k: torch.empty_like(h[k]).pin_memory() for k in ("pose", "root", "trans", "betas")}
     del prob, pb_ch, pb_mk, state, graphs
     torch.cuda.empty_cache()
 
@@ -530,7 +531,10 @@ def run_fit(args, rank, world, local, dev, light=False):
         else:
             vi = vidx
         fitm.optim_markers(mk, pose, opose, bt, o_betas, rt, tr, vi, None, smpl, cfg, problem=p, groups=groups)
-        return [x.to("cpu", non_blocking=False) for x in (pose, rt, tr, bt)]
+        for k, x in (("pose", pose), ("root", rt), ("trans", tr), ("betas", bt)):     # fitted parameters -> pinned host
+            h_out[k].copy_(x, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return h_out
 
     e2e_once()
     barrier()
@@ -538,9 +542,12 @@ def run_fit(args, rank, world, local, dev, light=False):
     e2e_once()
     barrier()
     t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    e2e_ranks = [float(t.item())]
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
+        every = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(every, t)
+        e2e_ranks = [float(x.item()) for x in every]
+    e2e_s = max(e2e_ranks)
     e2e_value = frames_global * K / e2e_s
     clocks = sampler.stop() if sampler else None
 
@@ -609,7 +616,7 @@ def run_fit(args, rank, world, local, dev, light=False):
                                  ("torch.distributed" if shard_fit.world > 1 else "none (one shard)"))},
             "stages": stage_rates(), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
-                    "seconds": e2e_s,
+                    "seconds": e2e_s, "seconds_per_rank": e2e_ranks,
                     "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d + %d Adam "
                             "iterations, one H2D of this rank's capture and one D2H of its fitted parameters per call" % (n_ch, n_mk)},
             "gpu_launches": launches, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "torch_gpu_baseline": tg,

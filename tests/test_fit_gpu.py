@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import rel_err
+from conftest import frame_rel_err, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -38,9 +38,14 @@ def test_chamfer_closure_golden(ctx, golden):
     loss2 = chamfer_closure(prob, pb, _T(g["ch_root"]).cuda(), losses)      # second call starts from the first one's matches
     assert abs(float(loss2) - float(loss)) <= 1e-6 * abs(float(loss))
     assert np.array_equal(prob.idx.cpu().numpy().astype(np.int64)[on], g["ch_idx"][on])
+    r = golden("closure_ref.npz")      # the same closure evaluated by the REFERENCE'S OWN SOURCE (optimization.py:147-285)
+    assert abs(float(loss) - float(r["ch_loss"])) <= 1e-5 * abs(float(r["ch_loss"]))
     for k, ref in (("pose_body", "ch_g_pose"), ("betas", "ch_g_betas"), ("trans", "ch_g_trans"), ("z_angle", "ch_g_z")):
         got = pb.gviews[k].cpu().numpy().reshape(g[ref].shape)
         assert rel_err(got, g[ref]) < 1e-4, k
+        assert rel_err(got, r[ref]) < 1e-4, k
+        if k != "betas":
+            assert frame_rel_err(got, r[ref]) < 1e-4, k      # normalised frame by frame
 
 
 def test_marker_closure_golden(ctx, golden):
@@ -53,9 +58,14 @@ def test_marker_closure_golden(ctx, golden):
     losses = {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0, "temporal": 1.0}
     loss = marker_closure(prob, pb, _T(g["mk_vidx"]).to(torch.int32).cuda(), losses)
     assert abs(float(loss) - float(g["mk_loss"])) <= 1e-5 * abs(float(g["mk_loss"]))
+    r = golden("closure_ref.npz")      # optim_markers compiled from the reference's source (optimization.py:288-399)
+    assert abs(float(loss) - float(r["mk_loss"])) <= 1e-5 * abs(float(r["mk_loss"]))
     for k, ref in (("pose_body", "mk_g_pose"), ("betas", "mk_g_betas"), ("trans", "mk_g_trans"), ("root_orient", "mk_g_root")):
         got = pb.gviews[k].cpu().numpy().reshape(g[ref].shape)
         assert rel_err(got, g[ref]) < 1e-4, k
+        assert rel_err(got, r[ref]) < 1e-4, k
+        if k != "betas":
+            assert frame_rel_err(got, r[ref]) < 1e-4, k
 
 
 def test_compute_nearest_points(ctx, golden):
@@ -75,6 +85,21 @@ def test_compute_nearest_points(ctx, golden):
     for m in np.where(idx != idx_ref)[0]:
         assert abs(mean_ref[m, idx[m]] - mean_ref[m, idx_ref[m]]) <= 1e-6 * mean_ref[m, idx_ref[m]]
     assert (idx == idx_ref).mean() > 0.9
+    r = golden("closure_ref.npz")          # compute_nearest_points compiled from the reference's source (:402-642)
+    assert np.array_equal(r["np_img_mask"], img_mask.numpy())
+    for m in np.where(idx != r["np_vertex_idx"])[0]:
+        assert abs(mean_ref[m, idx[m]] - mean_ref[m, r["np_vertex_idx"][m]]) <= 1e-6 * mean_ref[m, idx_ref[m]]
+
+
+def test_optim_chamfer_bakes_yaw_like_the_reference(ctx, golden):
+    """optim_chamfer with zero iterations of change: root_orient[:] = Rz(z) @ root_orient (optimization.py:280-285),
+    against the tensor the reference's own function left behind."""
+    from uuo_mocap_b200.fit import rot_z
+    g, r = golden("closure_top4.npz"), golden("closure_ref.npz")
+    z = _T(g["ch_z"]).cuda()
+    baked = (rot_z(z.view(-1, 1, 1)) @ _T(g["ch_root"]).cuda()).cpu().numpy()
+    assert rel_err(baked, r["ch_root_baked"]) < 1e-6
+    assert rel_err(rot_z(_T(r["rot_z_angles"]).cuda()).cpu().numpy(), r["rot_z"]) < 1e-6
 
 
 def _setup_fit(ctx, F, seed, n_ghost=2, dropout=0.1):

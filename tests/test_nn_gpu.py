@@ -54,14 +54,21 @@ def test_chamfer_smoke_seed(golden):
     assert abs(val - ref) <= 1e-6 * abs(ref)
 
 
-def test_mean_distance_argmin(get_model):
+@pytest.mark.parametrize("F,M,V", [(9, 13, 700), (1, 1, 1), (2, 3, 48), (17, 45, 6890), (33, 64, 97), (16, 70, 500)])
+def test_mean_distance_argmin(get_model, F, M, V):
+    """uuo_mean_dist_accumulate (one pass, packed fp32x2 arithmetic, sqrt.rn spelled out): acc BIT-equal to numpy's
+    fp32 reduction in frame order, incl. odd frame counts, masked frames, ragged M / V, a marker exactly on a vertex
+    (sqrt(0)) and dropped markers at the origin."""
     from uuo_mocap_b200 import ops
-    rng = np.random.default_rng(3)
-    F, M, V = 9, 13, 700
+    rng = np.random.default_rng(3 + F)
     v = rng.normal(0, 0.5, size=(F, V, 3)).astype(np.float32)
     m = rng.normal(0, 0.5, size=(F, M, 3)).astype(np.float32)
+    m[0, 0] = v[0, V // 2]                       # distance exactly 0 -> the scalar sqrt path
+    if F > 2:
+        m[2, M // 2] = 0.0                       # a dropped marker
     fm = np.ones(F, dtype=np.float32)
-    fm[[2, 5]] = 0
+    if F > 5:
+        fm[[2, 5]] = 0
     sel = np.where(fm == 1)[0]
     acc = np.zeros((M, V), dtype=np.float32)
     for f in sel:   # optimization.py:479-486,596-599 (numpy fp32, frames added in order)
@@ -72,6 +79,14 @@ def test_mean_distance_argmin(get_model):
                                             torch.from_numpy(fm).cuda())
     assert np.array_equal(acc_gpu.cpu().numpy(), acc)
     assert np.array_equal(idx.cpu().numpy().astype(np.int64), idx_ref)
+    # accumulating in two calls (frame ranges in order) is the same sum
+    if F >= 4:
+        h = F // 2
+        _, a2 = ops.mean_distance_argmin(torch.from_numpy(m[:h]).cuda(), torch.from_numpy(v[:h]).cuda(),
+                                         torch.from_numpy(fm[:h]).cuda(), finalize=False)
+        _, a2 = ops.mean_distance_argmin(torch.from_numpy(m[h:]).cuda(), torch.from_numpy(v[h:]).cuda(),
+                                         torch.from_numpy(fm[h:]).cuda(), acc=a2, finalize=False)
+        assert np.array_equal(a2.cpu().numpy(), acc)
 
 
 # ---- pruned (box-bounded) kernel: same outputs bit for bit, for ANY permutation ----

@@ -177,3 +177,46 @@ def test_find_best_part_fits(ctx):
     assert out["trans"].shape == (F, 3) and out["betas"].shape == (1, 10) and out["root_orient"].shape == (F, 1, 3, 3)
     assert out["aabb_volume_ratio"].shape == (F,) and torch.allclose(out["aabb_volume_ratio"].cpu(), torch.ones(F))
     assert out["markers_subset"].shape == markers.shape
+
+
+def test_part_fits_match_reference_source(ctx, golden):
+    """find_best_part_fits / closure_fit_subtree against the outputs of the REFERENCE'S OWN SOURCE
+    (markers_utils.py:274-638 compiled unmodified, oracle/gen_golden_ref_closures.py): (A) every candidate's closure at
+    z = 0.2 -- loss 1e-5, gradients 1e-4; (B) the function run with no optimiser step: same candidate order, same
+    three best scores (printed by the reference with 6 decimals), same winner, labels, weights and box ratio."""
+    from uuo_mocap_b200 import losses, parts
+    from uuo_mocap_b200.fit import rot_z
+    model, smpl, _ = ctx
+    r = golden("closure_ref.npz")
+    vlab = np.argmax(model.weights, axis=-1)
+    rot, mk = _T(r["pf_rot"]).cuda(), _T(r["pf_markers"]).cuda()
+    F = mk.shape[0]
+    assert parts.sub_hierarchies(np.array(model.parents), 3) == r["pf_subtrees"].tolist()
+    ob = _T(r["pf_betas"]).cuda()
+    for s, subtree in enumerate(r["pf_subtrees"]):
+        vidx = torch.from_numpy(np.concatenate([np.where(vlab == j)[0] for j in subtree])).cuda()
+        z = torch.full((1, 1, 1), 0.2, device="cuda", requires_grad=True)
+        tr = torch.median(mk, dim=1)[0].clone().requires_grad_(True)
+        betas = ob.clone().requires_grad_(True)
+        o = smpl(betas=betas.expand(F, -1), body_pose=rot[:, 1:], global_orient=rot_z(z.expand(F, 1, 1)) @ rot[:, :1], transl=tr,
+                 pose2rot=False)
+        loss = losses.chamfer_distance(mk, o.vertices[:, vidx], single_directional=True)[0] * 10.0
+        loss = loss + torch.nn.functional.mse_loss(betas, ob) * 0.1
+        loss.backward()
+        assert abs(float(loss) - float(r["pfA_loss"][s])) <= 1e-5 * abs(float(r["pfA_loss"][s])), subtree
+        assert rel_err(z.grad.cpu().numpy().reshape(-1), r["pfA_g_z"][s]) < 1e-4
+        assert rel_err(tr.grad.cpu().numpy(), r["pfA_g_trans"][s]) < 1e-4
+        assert rel_err(betas.grad.cpu().numpy(), r["pfA_g_betas"][s]) < 1e-4
+    cfg = {"optimizer": {"name": "lbfgs", "tolerance_grad": 1e-7, "tolerance_change": 1e-9},
+           "stages": {"part": {"mode": "cluster", "num_iters": 0, "losses": {"chamfer": 10.0, "reg_betas": 0.1}}}}
+    out = parts.find_best_part_fits(mk, rot[:, 1:], ob, rot[:, :1], torch.from_numpy(r["pf_labels"]), smpl, model.parents, cfg)
+    rank = out["ranking"]
+    assert [list(j) for j, _ in rank[:3]] == r["pfB_top3_joints"].tolist()
+    for (_, d), ref in zip(rank[:3], r["pfB_top3_dist"]):
+        assert abs(d - ref) <= 1e-6 + 1e-5 * ref
+    assert out["chain"].tolist() == r["pfB_chain"].tolist()
+    assert np.array_equal(out["marker_labels"].cpu().numpy(), r["pfB_marker_labels"])
+    assert rel_err(out["marker_weights"].cpu().numpy(), r["pfB_marker_weights"]) < 1e-6
+    assert rel_err(out["aabb_volume_ratio"].cpu().numpy(), r["pfB_aabb"]) < 1e-6
+    assert rel_err(out["trans"].cpu().numpy(), r["pfB_trans"]) < 1e-6
+    assert rel_err(out["root_orient"].cpu().numpy(), r["pfB_root"]) < 1e-6
