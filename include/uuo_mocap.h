@@ -203,7 +203,10 @@ int uuo_transvel_accumulate(const float* trans, const float* mm, const float* pr
  *   uuo_comm_connect_local   peers[world] created in THIS process (tests, or one process driving several GPUs)
  *   uuo_comm_all_reduce_sum  x[n] (n <= 1024) <- sum over ranks, added in rank order on every rank
  *   uuo_comm_halo_exchange   x[F,D]: prev[r*ld + col + d] <- the left neighbour's last n rows, next[...] <- the right
- *                            neighbour's first n rows (n*D <= 1024); prev / next untouched at the ends of the sequence */
+ *                            neighbour's first n rows (n*D <= 1024); prev / next untouched at the ends of the sequence
+ *   uuo_comm_group_*         the same two exchanges for ALL ranks of a world that lives on one device, as ONE cooperative
+ *                            launch (block r = rank r): separate launches that wait on one another are not guaranteed to be
+ *                            co-resident on one GPU.  comms[world] linked with uuo_comm_connect_local; arrays indexed by rank */
 typedef struct uuo_comm uuo_comm;
 int uuo_comm_create(int rank, int world, int device, uuo_comm** out);
 int uuo_comm_set_timeout(uuo_comm* c, double seconds);   /* a wait on a peer longer than this traps (default 60 s) */
@@ -215,6 +218,9 @@ void uuo_comm_destroy(uuo_comm* c);
 int uuo_comm_all_reduce_sum(uuo_comm* c, float* x, int n, void* stream);
 int uuo_comm_halo_exchange(uuo_comm* c, const float* x, int F, int D, int n, float* prev, float* next, int ld, int col,
                            void* stream);
+int uuo_comm_group_all_reduce_sum(uuo_comm* const* comms, float* const* xs, int n, int world, void* stream);
+int uuo_comm_group_halo_exchange(uuo_comm* const* comms, const float* const* xs, const int* Fs, int D, int n,
+                                 float* const* prevs, float* const* nexts, int ld, int col, int world, void* stream);
 
 /* ---- fused Adam over a flat parameter block (north-star optimiser; torch.optim.Adam semantics) */
 int uuo_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr,

@@ -2,8 +2,10 @@
 
 Every multi-GPU fitting number runs through (1) the prev/next halo branches of the temporal / trans_vel kernels,
 (2) global normalisers, (3) the per-iteration [d betas | loss] sum and (4) the per-range [M,V] mean-distance sums.
-Here a sequence is cut into 2 and 3 frame ranges, each range is driven as its own "rank" (own FitProblem, own CUDA
-stream, own PeerComm mailbox linked with uuo_comm_connect_local), and the result must equal the unsharded CUDA closure
+Here a sequence is cut into 2 and 3 frame ranges, each range is driven as its own "rank" (own FitProblem, own Python
+thread, own PeerComm mailbox; dist.LocalGroup turns every exchange into one cooperative launch that plays all ranks,
+because separate launches that wait on one another are not guaranteed to be co-resident on one GPU), and the result
+must equal the unsharded CUDA closure
 (per-frame gradients bit for bit: the per-frame arithmetic does not depend on the cut) and the oracle closure."""
 import numpy as np
 import pytest
@@ -91,41 +93,36 @@ def test_transvel_kernel_halo_rows(world):
     assert abs(float(loss) - float(loss_ref)) <= 1e-6 * float(loss_ref)
 
 
-def _local_shards(world, dev="cuda:0"):
-    from uuo_mocap_b200.dist import PeerComm, Shard
-    comms = [PeerComm(r, world, dev, timeout_s=10.0) for r in range(world)]
-    PeerComm.connect_local(comms)
-    return [Shard(r, world, None, comms[r]) for r in range(world)], comms
-
-
 @pytest.mark.parametrize("world", [2, 3])
 def test_peer_comm_sum_and_halo(world):
-    """uuo_comm_all_reduce_sum / uuo_comm_halo_exchange between `world` mailboxes on one GPU, several epochs."""
-    shards, comms = _local_shards(world)
-    streams = [torch.cuda.Stream() for _ in range(world)]
+    """The mailbox protocol of csrc/peer.cu (epochs, parity double-buffering, flags) over several epochs: all ranks of
+    a world on one GPU run as ONE cooperative launch per exchange (uuo_comm_group_*, block r = rank r)."""
+    from uuo_mocap_b200.dist import LocalGroup
+    grp = LocalGroup(world, "cuda:0")
     g0 = torch.Generator().manual_seed(7)
     F, D = 9, 207
     xs = [torch.randn(F + r, D, generator=g0).cuda() for r in range(world)]
+
+    def rank_fn(r):
+        res = []
+        for epoch in range(5):
+            red = torch.full((2, 16), float(r + 1 + epoch), device="cuda")
+            prev = torch.zeros(2, D + 3, device="cuda") if r > 0 else None
+            nxt = torch.zeros(2, D + 3, device="cuda") if r < world - 1 else None
+            grp.comms[r].all_reduce_sum_(red)
+            grp.comms[r].halo_exchange(xs[r], 2, prev, nxt, col=3)
+            res.append((red, prev, nxt))
+        return res
+    out = grp.run(rank_fn)
     torch.cuda.synchronize()
-    for epoch in range(5):
-        reds = [torch.full((2, 16), float(r + 1 + epoch), device="cuda") for r in range(world)]
-        prevs = [torch.zeros(2, D, device="cuda") for _ in range(world)]
-        nxts = [torch.zeros(2, D, device="cuda") for _ in range(world)]
-        torch.cuda.synchronize()
-        for r in range(world):
-            with torch.cuda.stream(streams[r]):
-                comms[r].all_reduce_sum_(reds[r])
-                comms[r].halo_exchange(xs[r], 2, prevs[r] if r > 0 else None, nxts[r] if r < world - 1 else None)
-        torch.cuda.synchronize()
-        want = float(sum(r + 1 + epoch for r in range(world)))
-        for r in range(world):
-            assert torch.all(reds[r] == want)
+    for r in range(world):
+        for epoch, (red, prev, nxt) in enumerate(out[r]):
+            assert torch.all(red == float(sum(q + 1 + epoch for q in range(world))))
             if r > 0:
-                assert torch.equal(prevs[r], xs[r - 1][-2:])
+                assert torch.equal(prev[:, 3:], xs[r - 1][-2:]) and float(prev[:, :3].abs().sum()) == 0.0
             if r < world - 1:
-                assert torch.equal(nxts[r], xs[r + 1][:2])
-    for c in comms:
-        c.close()
+                assert torch.equal(nxt[:, 3:], xs[r + 1][:2])
+    grp.close()
 
 
 def _closure_inputs(golden):
@@ -142,8 +139,9 @@ def _run_sharded(ctx, golden, world, stage, transport):
     g, F = _closure_inputs(golden)
     mk_all = _T(g["markers"])
     wsum = float(ops.get_marker_mask(mk_all.cuda()).sum())
-    shards, comms = _local_shards(world)
-    streams = [torch.cuda.Stream() for _ in range(world)]
+    from uuo_mocap_b200.dist import LocalGroup
+    grp = LocalGroup(world, "cuda:0")
+    shards = [grp.shard(r) for r in range(world)]
     probs, pbs, extra = [], [], []
     for r, (lo, hi) in enumerate(_ranges(F, world)):
         sl = slice(lo, hi)
@@ -158,24 +156,25 @@ def _run_sharded(ctx, golden, world, stage, transport):
                                          "root_orient": _T(g["mk_root"][sl]), "trans": _T(g["ch_trans"][sl])}, "cuda:0"))
             extra.append(_T(g["mk_vidx"]).to(torch.int32).cuda())
     torch.cuda.synchronize()
-    out = [None] * world
-    for rep in range(2):                      # twice: the second evaluation runs on the next mailbox epochs
-        for r in range(world):
-            with torch.cuda.stream(streams[r]):
-                if stage == "chamfer":
-                    out[r] = chamfer_closure(probs[r], pbs[r], extra[r],
-                                             {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0, "trans_vel": 1.0})
-                else:
-                    out[r] = marker_closure(probs[r], pbs[r], extra[r],
-                                            {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0, "temporal": 1.0})
-        torch.cuda.synchronize()
+
+    def rank_fn(r):
+        o = None
+        for rep in range(2):                  # twice: the second evaluation runs on the next mailbox epochs
+            if stage == "chamfer":
+                o = chamfer_closure(probs[r], pbs[r], extra[r],
+                                    {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0, "trans_vel": 1.0})
+            else:
+                o = marker_closure(probs[r], pbs[r], extra[r],
+                                   {"marker": 1.0, "reg_pose_body": 0.1, "reg_betas": 1.0, "temporal": 1.0})
+        return o
+    out = grp.run(rank_fn)
+    torch.cuda.synchronize()
     losses = [float(o) for o in out]
     keys = ("pose_body", "trans", "z_angle") if stage == "chamfer" else ("pose_body", "trans", "root_orient")
     grads = {k: torch.cat([pb.gviews[k] for pb in pbs]).cpu().numpy() for k in keys}
     gb = [pb.gviews["betas"].cpu().numpy() for pb in pbs]
     idx = torch.cat([p.idx for p in probs]).cpu().numpy()
-    for c in comms:
-        c.close()
+    grp.close()
     return losses, grads, gb, idx
 
 
@@ -301,17 +300,15 @@ def test_stacked_hypotheses_sharded(ctx):
     gb_c = c1.gviews["betas"].cpu().numpy().copy()
     l_m = float(marker_closure(p1, m1, vall, lm))
     gb_m = m1.gviews["betas"].cpu().numpy().copy()
-    shards, comms = _local_shards(world)
-    streams = [torch.cuda.Stream() for _ in range(world)]
-    built = [build(slice(lo, hi), shards[r], F, wsum) for r, (lo, hi) in enumerate(_ranges(F, world))]
+    from uuo_mocap_b200.dist import LocalGroup
+    grp = LocalGroup(world, "cuda:0")
+    built = [build(slice(lo, hi), grp.shard(r), F, wsum) for r, (lo, hi) in enumerate(_ranges(F, world))]
     torch.cuda.synchronize()
-    res = []
-    for r in range(world):
-        with torch.cuda.stream(streams[r]):
-            p, c, m, rt = built[r]
-            a = chamfer_closure(p, c, rt, lc)
-            b = marker_closure(p, m, vall, lm)
-            res.append((a, b))
+
+    def rank_fn(r):
+        p, c, m, rt = built[r]
+        return chamfer_closure(p, c, rt, lc), marker_closure(p, m, vall, lm)
+    res = grp.run(rank_fn)
     torch.cuda.synchronize()
     for r in range(world):
         p, c, m, rt = built[r]
@@ -320,5 +317,4 @@ def test_stacked_hypotheses_sharded(ctx):
         assert rel_err(m.gviews["betas"].cpu().numpy(), gb_m) < 1e-5
         assert rel_err(c.gviews["betas"].cpu().numpy(), gb_c) < 1e-5
     assert l_c > 0
-    for c in comms:
-        c.close()
+    grp.close()

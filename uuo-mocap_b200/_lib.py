@@ -59,6 +59,9 @@ SIGNATURES = {
     "uuo_comm_destroy": (None, [_P]),
     "uuo_comm_all_reduce_sum": (_I, [_P, _P, _I, _P]),
     "uuo_comm_halo_exchange": (_I, [_P, _P, _I, _I, _I, _P, _P, _I, _I, _P]),
+    "uuo_comm_group_all_reduce_sum": (_I, [C.POINTER(_P), C.POINTER(_P), _I, _I, _P]),
+    "uuo_comm_group_halo_exchange": (_I, [C.POINTER(_P), C.POINTER(_P), C.POINTER(_I), _I, _I, C.POINTER(_P), C.POINTER(_P),
+                                          _I, _I, _I, _P]),
     "uuo_adam_step": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _I, _P]),
     "uuo_adam_step_dev": (_I, [_P, _P, _P, _P, _SZ, _F, _F, _F, _F, _P, _P]),
 }

@@ -63,9 +63,8 @@ __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t e, unsigne
 }
 
 // x[n] <- sum over ranks of x[n], summed in rank order on every rank (identical bits everywhere)
-__global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
-                                                              float* __restrict__ x, int n,
-                                                              unsigned long long timeout_ns) {
+__device__ __forceinline__ void all_reduce_body(const PeerTable& peers, Mailbox* mine, int rank, int world,
+                                                float* __restrict__ x, int n, unsigned long long timeout_ns) {
   const uint32_t e = mine->ar_epoch + 1;
   const int par = e & 1;
   for (int p = 0; p < world; ++p) {
@@ -88,11 +87,16 @@ __global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, M
   if (threadIdx.x == 0) mine->ar_epoch = e;
 }
 
+__global__ void __launch_bounds__(256) comm_all_reduce_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
+                                                              float* __restrict__ x, int n,
+                                                              unsigned long long timeout_ns) {
+  all_reduce_body(peers, mine, rank, world, x, n, timeout_ns);
+}
+
 // prev[r*ld + col + d] <- row (F_left - n + r) of the left neighbour, next[...] <- row r of the right neighbour
-__global__ void __launch_bounds__(256) comm_halo_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
-                                                        const float* __restrict__ x, int F, int D, int n,
-                                                        float* __restrict__ prev, float* __restrict__ next, int ld,
-                                                        int col, unsigned long long timeout_ns) {
+__device__ __forceinline__ void halo_body(const PeerTable& peers, Mailbox* mine, int rank, int world,
+                                          const float* __restrict__ x, int F, int D, int n, float* __restrict__ prev,
+                                          float* __restrict__ next, int ld, int col, unsigned long long timeout_ns) {
   const uint32_t e = mine->halo_epoch + 1;
   const int par = e & 1;
   const int cnt = n * D;
@@ -124,6 +128,38 @@ __global__ void __launch_bounds__(256) comm_halo_kernel(PeerTable peers, Mailbox
   }
   __syncthreads();
   if (threadIdx.x == 0) mine->halo_epoch = e;
+}
+
+__global__ void __launch_bounds__(256) comm_halo_kernel(PeerTable peers, Mailbox* mine, int rank, int world,
+                                                        const float* __restrict__ x, int F, int D, int n,
+                                                        float* __restrict__ prev, float* __restrict__ next, int ld,
+                                                        int col, unsigned long long timeout_ns) {
+  halo_body(peers, mine, rank, world, x, F, D, n, prev, next, ld, col, timeout_ns);
+}
+
+// ---- all ranks of a world that lives on ONE device, as ONE cooperative launch: block r plays rank r -------------
+// Separate launches that wait on one another are not guaranteed to run at the same time on one GPU, so a process that
+// drives several shards of one device (the single-GPU parity tests) runs the exchange of all its ranks in one grid
+// whose blocks are co-resident by construction.  Same mailboxes, epochs, flags and code as the per-rank kernels.
+struct GroupArgs {
+  PeerTable peers;                       // the same table on every rank (all mailboxes are local)
+  float* x[UUO_COMM_MAXW];
+  const float* hx[UUO_COMM_MAXW];
+  float* prev[UUO_COMM_MAXW];
+  float* next[UUO_COMM_MAXW];
+  int F[UUO_COMM_MAXW];
+};
+
+__global__ void __launch_bounds__(256) comm_group_all_reduce_kernel(GroupArgs a, int world, int n,
+                                                                    unsigned long long timeout_ns) {
+  const int r = blockIdx.x;
+  all_reduce_body(a.peers, a.peers.p[r], r, world, a.x[r], n, timeout_ns);
+}
+
+__global__ void __launch_bounds__(256) comm_group_halo_kernel(GroupArgs a, int world, int D, int n, int ld, int col,
+                                                              unsigned long long timeout_ns) {
+  const int r = blockIdx.x;
+  halo_body(a.peers, a.peers.p[r], r, world, a.hx[r], a.F[r], D, n, a.prev[r], a.next[r], ld, col, timeout_ns);
 }
 
 extern "C" int uuo_comm_create(int rank, int world, int device, uuo_comm** out) {
@@ -249,5 +285,55 @@ extern "C" int uuo_comm_halo_exchange(uuo_comm* c, const float* x, int F, int D,
   comm_halo_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(c->peers, c->mine, c->rank, c->world, x, F, D, n, prev, next,
                                                         ld, col, c->timeout_ns);
   UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+static int group_check(uuo_comm* const* comms, int world) {
+  UUO_CHECK_ARG(comms && world >= 1 && world <= UUO_COMM_MAXW, "bad arguments");
+  for (int r = 0; r < world; ++r) {
+    UUO_CHECK_ARG(comms[r] && comms[r]->rank == r && comms[r]->world == world && comms[r]->connected,
+                  "comms[r] must be the connected rank r of this world");
+    UUO_CHECK_ARG(comms[r]->device == comms[0]->device, "a group launch needs every rank on one device");
+  }
+  return UUO_OK;
+}
+
+extern "C" int uuo_comm_group_all_reduce_sum(uuo_comm* const* comms, float* const* xs, int n, int world, void* stream) {
+  int rc = group_check(comms, world);
+  if (rc) return rc;
+  UUO_CHECK_ARG(xs && n >= 0 && n <= UUO_COMM_MAXRED, "n must be <= 1024 floats");
+  if (world == 1 || n == 0) return UUO_OK;
+  GroupArgs a;
+  memset(&a, 0, sizeof(a));
+  a.peers = comms[0]->peers;
+  for (int r = 0; r < world; ++r) { UUO_CHECK_ARG(xs[r], "xs[r] is NULL"); a.x[r] = xs[r]; }
+  unsigned long long to = comms[0]->timeout_ns;
+  void* args[] = {&a, &world, &n, &to};
+  UUO_CUDA(cudaLaunchCooperativeKernel((const void*)comm_group_all_reduce_kernel, dim3(world), dim3(256), args, 0,
+                                       (cudaStream_t)stream));
+  return UUO_OK;
+}
+
+extern "C" int uuo_comm_group_halo_exchange(uuo_comm* const* comms, const float* const* xs, const int* Fs, int D, int n,
+                                            float* const* prevs, float* const* nexts, int ld, int col, int world,
+                                            void* stream) {
+  int rc = group_check(comms, world);
+  if (rc) return rc;
+  UUO_CHECK_ARG(xs && Fs && prevs && nexts, "NULL pointer");
+  UUO_CHECK_ARG(n >= 1 && D >= 1 && (size_t)n * D <= UUO_COMM_MAXHALO, "halo must be <= 1024 floats");
+  UUO_CHECK_ARG(ld >= col + D && col >= 0, "bad ld / col");
+  if (world == 1) return UUO_OK;
+  GroupArgs a;
+  memset(&a, 0, sizeof(a));
+  a.peers = comms[0]->peers;
+  for (int r = 0; r < world; ++r) {
+    UUO_CHECK_ARG(xs[r] && Fs[r] >= n, "every shard must hold at least n frames");
+    UUO_CHECK_ARG((r == 0 || prevs[r]) && (r + 1 == world || nexts[r]), "prev / next buffer is NULL");
+    a.hx[r] = xs[r]; a.F[r] = Fs[r]; a.prev[r] = prevs[r]; a.next[r] = nexts[r];
+  }
+  unsigned long long to = comms[0]->timeout_ns;
+  void* args[] = {&a, &world, &D, &n, &ld, &col, &to};
+  UUO_CUDA(cudaLaunchCooperativeKernel((const void*)comm_group_halo_kernel, dim3(world), dim3(256), args, 0,
+                                       (cudaStream_t)stream));
   return UUO_OK;
 }

@@ -38,6 +38,7 @@ class PeerComm:
         h = C.c_void_p()
         _lib.check(_lib.lib().uuo_comm_create(self.rank, self.world, self.device.index or 0, C.byref(h)))
         self.handle = h
+        self.group = None                     # LocalGroup when one process drives every rank of the world on one device
         if timeout_s is not None:
             _lib.check(_lib.lib().uuo_comm_set_timeout(h, float(timeout_s)))
 
@@ -65,6 +66,8 @@ class PeerComm:
     def all_reduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
         if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
             raise self._lib.UuoError("PeerComm.all_reduce_sum_ needs a contiguous fp32 CUDA tensor")
+        if self.group is not None:
+            return self.group.all_reduce_sum_(self.rank, t)
         self._lib.check(self._lib.lib().uuo_comm_all_reduce_sum(self.handle, self._lib.ptr(t), t.numel(),
                                                                   self._lib.stream_ptr(t.device)))
         return t
@@ -75,6 +78,8 @@ class PeerComm:
         F, D = x.shape
         ref = prev if prev is not None else nxt
         ld = ref.shape[1] if ref is not None else D
+        if self.group is not None:
+            return self.group.halo_exchange(self.rank, x, n, prev, nxt, ld, col)
         self._lib.check(self._lib.lib().uuo_comm_halo_exchange(self.handle, self._lib.ptr(x), F, D, n,
                                                                  self._lib.ptr(prev), self._lib.ptr(nxt), ld, col,
                                                                  self._lib.stream_ptr(x.device)))
@@ -83,6 +88,94 @@ class PeerComm:
         if self.handle:
             self._lib.lib().uuo_comm_destroy(self.handle)
             self.handle = None
+
+
+class LocalGroup:
+    """Every rank of a world driven by ONE process on ONE device (the single-GPU parity tests of the sharded closures).
+    Each rank runs in its own Python thread (``run``) and issues its kernels on the same CUDA stream; an exchange is a
+    host barrier, ONE cooperative launch that plays all ranks (uuo_comm_group_*: block r = rank r, same mailboxes and
+    protocol as the per-rank kernels), and a second barrier.  Kernels of different launches never wait on one another."""
+
+    def __init__(self, world: int, device, timeout_s: Optional[float] = 20.0):
+        import threading
+        self.world = int(world)
+        self.device = torch.device(device)
+        self.comms = [PeerComm(r, world, device, timeout_s) for r in range(world)]
+        PeerComm.connect_local(self.comms)
+        for c in self.comms:
+            c.group = self
+        self._barrier = threading.Barrier(world)
+        self._slot = [None] * world
+
+    def shard(self, rank: int) -> "Shard":
+        return Shard(rank, self.world, None, self.comms[rank])
+
+    def _collect(self, rank, item, launch):
+        self._slot[rank] = item
+        self._barrier.wait()
+        if rank == 0:
+            try:
+                launch(list(self._slot))
+            except BaseException:
+                self._barrier.abort()
+                raise
+        self._barrier.wait()
+
+    def all_reduce_sum_(self, rank: int, t: torch.Tensor) -> torch.Tensor:
+        import ctypes as C
+        lib = self.comms[0]._lib
+
+        def launch(ts):
+            n = ts[0].numel()
+            if any(x.numel() != n for x in ts):
+                raise ValueError("every rank must reduce the same number of floats")
+            cs = (C.c_void_p * self.world)(*[c.handle for c in self.comms])
+            xs = (C.c_void_p * self.world)(*[x.data_ptr() for x in ts])
+            lib.check(lib.lib().uuo_comm_group_all_reduce_sum(cs, xs, n, self.world, lib.stream_ptr(self.device)))
+        self._collect(rank, t, launch)
+        return t
+
+    def halo_exchange(self, rank: int, x, n, prev, nxt, ld, col) -> None:
+        import ctypes as C
+        lib = self.comms[0]._lib
+
+        def launch(items):
+            D = items[0][0].shape[1]
+            ptr_of = lambda t: None if t is None else t.data_ptr()
+            cs = (C.c_void_p * self.world)(*[c.handle for c in self.comms])
+            xs = (C.c_void_p * self.world)(*[it[0].data_ptr() for it in items])
+            Fs = (C.c_int * self.world)(*[it[0].shape[0] for it in items])
+            ps = (C.c_void_p * self.world)(*[ptr_of(it[1]) for it in items])
+            ns = (C.c_void_p * self.world)(*[ptr_of(it[2]) for it in items])
+            lib.check(lib.lib().uuo_comm_group_halo_exchange(cs, xs, Fs, D, n, ps, ns, ld, col, self.world,
+                                                             lib.stream_ptr(self.device)))
+        self._collect(rank, (x, prev, nxt), launch)
+
+    def run(self, fn):
+        """fn(rank) on one thread per rank; returns the list of results (re-raises the first failure)."""
+        import threading
+        out, err = [None] * self.world, [None] * self.world
+
+        def work(r):
+            try:
+                with torch.cuda.device(self.device):
+                    out[r] = fn(r)
+            except BaseException as e:      # a failed rank must not leave the others waiting at a barrier
+                err[r] = e
+                self._barrier.abort()
+        ts = [threading.Thread(target=work, args=(r,)) for r in range(self.world)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        real = [e for e in err if e is not None and not isinstance(e, threading.BrokenBarrierError)]
+        if real or any(err):
+            raise (real[0] if real else [e for e in err if e is not None][0])
+        return out
+
+    def close(self):
+        for c in self.comms:
+            c.close()
 
 
 @dataclass
