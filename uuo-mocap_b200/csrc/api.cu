@@ -22,7 +22,7 @@ extern "C" int uuo_lbs_forward(const uuo_model* m, const float* betas, int betas
   cudaStream_t st = (cudaStream_t)stream;
   uuo_ws ws = carve_ws(m, F, workspace);
   if ((rc = launch_fk_forward(m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, transl, F, joints, ws, st))) return rc;
-  if ((rc = launch_vposed_gemm(m, F, ws, st))) return rc;
+  if ((rc = launch_vposed_gemm(m, F, ws, betas_rows == 1 ? betas : nullptr, st))) return rc;
   if ((rc = launch_skin_forward(m, transl, F, vertices, joints, ws, st))) return rc;
   return UUO_OK;
 }

@@ -80,6 +80,7 @@ struct uuo_ws {
   float* gbetas;  // [F][16]
   float* rowbuf;  // [F][R<=64][4]  scratch of the row-sparse paths
   float* Aimg;    // [ceil(F/16)][2][192*32] tf32 hi|lo swizzled image of the relative transforms (skin_tc.cu)
+  float* vshaped; // [NP]  v_template + shapedirs . betas when ONE betas row is shared by all frames (exact fp32)
   size_t total_floats;
 };
 
@@ -101,6 +102,7 @@ static inline uuo_ws carve_ws(const uuo_model* m, int F, void* base) {
   w.gbetas = take((size_t)F * 16);
   w.rowbuf = take((size_t)F * 64 * 4);
   w.Aimg = take((size_t)((F + 15) / 16) * 2 * 192 * 32);
+  w.vshaped = take((size_t)m->NP);
   w.total_floats = off;
   return w;
 }
@@ -162,9 +164,12 @@ int launch_fk_backward(const uuo_model* m, const float* betas, int betas_rows, c
                        float* g_betas, float* g_go, float* g_bp, float* g_yaw, float* g_transl, cudaStream_t st);
 // host: rows x K fp32 (K contiguous, pitch ld = K) -> [rows/NT][K/32][2][NT*32] swizzled tf32 hi|lo tiles
 void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int K, int NT);
-int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+// betas_shared != NULL: ONE betas row for all frames -> v_shaped is evaluated once in exact fp32 (launch_vshaped) and
+// only the pose rows go through the tensor cores
+int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st);
+int launch_vshaped(const uuo_model* m, const float* betas, const uuo_ws& ws, cudaStream_t st);
 int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st);
-int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st);
 int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int uuo_gcoef_splits(const uuo_model* m, int F);
 int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);

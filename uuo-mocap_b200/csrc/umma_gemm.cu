@@ -21,15 +21,22 @@ namespace {
 constexpr int BM = 128;             // rows of A per tile (frames)
 constexpr int BK = 32;              // fp32 elements per K block = one 128 B swizzle row
 constexpr int NT_MAX = 256;         // max columns per tile
-constexpr int STAGES = 2;
 constexpr int A_TILE_BYTES = BM * BK * 4;            // 16 KB (hi) + 16 KB (lo)
 constexpr int B_TILE_BYTES_MAX = NT_MAX * BK * 4;    // 32 KB (hi) + 32 KB (lo)
-constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + 2 * B_TILE_BYTES_MAX;   // 96 KB
+// 3 terms: a stage holds A hi|lo + B hi|lo = 96 KB -> 2 stages.  2 terms: B's lo half is never fetched, a stage is
+// 64 KB -> 3 stages, which is what hides the fill latency of a stage (split + store of A, L2 round trip of B) behind
+// the 8 MMAs of the other two
+template <int TERMS> struct Cfg {
+  static constexpr int STAGES = TERMS == 3 ? 2 : 3;
+  static constexpr int STAGE_BYTES = 2 * A_TILE_BYTES + (TERMS == 3 ? 2 : 1) * B_TILE_BYTES_MAX;
+};
 constexpr int EPI_WARPS = 4, PROD_WARPS = 8;
 constexpr int WARP_MMA = EPI_WARPS, WARP_BLOAD = EPI_WARPS + 1, WARP_PROD0 = EPI_WARPS + 2;
 constexpr int NTHREADS = (EPI_WARPS + 2 + PROD_WARPS) * 32;   // 448
 constexpr int STAGING_FLOATS = 32 * 32;              // per epilogue warp, XOR-swizzled transpose tile
-constexpr int SMEM_BYTES = 1024 /*align slack*/ + STAGES * STAGE_BYTES + EPI_WARPS * STAGING_FLOATS * 4 + 256;
+template <int TERMS> constexpr int smem_bytes() {
+  return 1024 /*align slack*/ + Cfg<TERMS>::STAGES * Cfg<TERMS>::STAGE_BYTES + EPI_WARPS * STAGING_FLOATS * 4 + 256;
+}
 
 struct GemmArgs {
   const float* A; long lda; int M;   // fp32 row-major, K contiguous
@@ -37,6 +44,8 @@ struct GemmArgs {
   float* C; long ldc; long split_stride;
   const float* bias;                 // [n_tiles*NT] or null
   int NT, n_tiles, m_tiles, kb_total, k_splits, kb_per_split, n_valid;
+  int terms;                         // 3: Ahi.Bhi + Alo.Bhi + Ahi.Blo;  2: B's lo half is neither fetched nor multiplied
+  int k_zero_from;                   // columns k >= this of A are read as 0 (-1: none)
 };
 
 __device__ __forceinline__ void decode_item(const GemmArgs& g, int w, int& mt, int& nt, int& ks) {
@@ -46,7 +55,9 @@ __device__ __forceinline__ void decode_item(const GemmArgs& g, int w, int& mt, i
   nt = r / g.k_splits;
 }
 
+template <int TERMS>
 __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g) {
+  constexpr int STAGES = Cfg<TERMS>::STAGES, STAGE_BYTES = Cfg<TERMS>::STAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = umma::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -98,6 +109,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         const int gr = mt * BM + row;
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (gr < g.M) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + (long)gr * g.lda + (long)kb * BK + c * 4));
+        if (g.k_zero_from >= 0) {
+          const int k0 = kb * BK + c * 4;
+          if (k0 + 3 >= g.k_zero_from) {
+            if (k0 >= g.k_zero_from) v[i].x = 0.f;
+            if (k0 + 1 >= g.k_zero_from) v[i].y = 0.f;
+            if (k0 + 2 >= g.k_zero_from) v[i].z = 0.f;
+            v[i].w = 0.f;
+          }
+        }
       }
       if (++kb >= kb_end) {
         w += gridDim.x;
@@ -153,9 +173,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % STAGES;
           umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
-          umma::mbar_arrive_expect_tx(FULL_B(s), 2 * b_tile_bytes);
+          const uint32_t nbytes = (TERMS == 3 ? 2u : 1u) * b_tile_bytes;       // hi | lo are contiguous: hi alone = first half
+          umma::mbar_arrive_expect_tx(FULL_B(s), nbytes);
           const float* src = g.Bimg + ((size_t)nt * g.kb_total + kb) * (size_t)(2 * g.NT * BK);
-          umma::bulk_g2s(base + s * STAGE_BYTES + 2 * A_TILE_BYTES, src, 2 * b_tile_bytes, FULL_B(s));
+          umma::bulk_g2s(base + s * STAGE_BYTES + 2 * A_TILE_BYTES, src, nbytes, FULL_B(s));
         }
       }
     }
@@ -185,7 +206,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
             const uint64_t dbh = umma::smem_desc_sw128(b_hi + k * 32), dbl = umma::smem_desc_sw128(b_lo + k * 32);
             umma::mma_tf32(d_tmem, dah, dbh, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             umma::mma_tf32(d_tmem, dal, dbh, idesc, 1u);
-            umma::mma_tf32(d_tmem, dah, dbl, idesc, 1u);
+            if (TERMS == 3) umma::mma_tf32(d_tmem, dah, dbl, idesc, 1u);
           }
           umma::mma_commit(EMPTY(s));                     // smem slot is free once these MMAs have read it
           if (kb + 1 == kb1) umma::mma_commit(TFULL(acc));   // accumulator complete
@@ -281,9 +302,15 @@ void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int 
 }
 
 static int launch_umma(const GemmArgs& g, cudaStream_t st) {
-  UUO_DYN_SMEM(umma_gemm_kernel, SMEM_BYTES);
   const int items = g.m_tiles * g.n_tiles * g.k_splits;
-  umma_gemm_kernel<<<std::min(items, uuo_sm_count()), NTHREADS, SMEM_BYTES, st>>>(g);
+  const int grid = std::min(items, uuo_sm_count());
+  if (g.terms == 2) {
+    UUO_DYN_SMEM(umma_gemm_kernel<2>, smem_bytes<2>());
+    umma_gemm_kernel<2><<<grid, NTHREADS, smem_bytes<2>(), st>>>(g);
+  } else {
+    UUO_DYN_SMEM(umma_gemm_kernel<3>, smem_bytes<3>());
+    umma_gemm_kernel<3><<<grid, NTHREADS, smem_bytes<3>(), st>>>(g);
+  }
   UUO_LAUNCH_CHECK();
   return UUO_OK;
 }
@@ -296,12 +323,38 @@ int uuo_gcoef_splits(const uuo_model* m, int F) {
   return (kbT + per - 1) / per;
 }
 
-int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
+// v_shaped[c] = v_template[c] + sum_l betas[l] shapedirs[c][l]  (lbs.py:209, 275-296) for ONE betas row, exact fp32
+__global__ void __launch_bounds__(256) vshaped_kernel(const float* __restrict__ vt, const float* __restrict__ Bmat, int NP,
+                                                      int P, int NB, const float* __restrict__ betas,
+                                                      float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= NP) return;
+  float a = 0.f;
+  for (int l = 0; l < NB; ++l) a = fmaf(__ldg(betas + l), Bmat[(size_t)(P + l) * NP + c], a);
+  out[c] = vt[c] + a;          // the offset first, then the template: the order of lbs.py:209 (v_template + blend_shapes)
+}
+
+int launch_vshaped(const uuo_model* m, const float* betas, const uuo_ws& ws, cudaStream_t st) {
+  vshaped_kernel<<<(m->NP + 255) / 256, 256, 0, st>>>(m->vt, m->Bmat, m->NP, m->P, m->NB, betas, ws.vshaped);
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st) {
   GemmArgs g;
   g.A = ws.coef; g.lda = m->KP; g.M = F;
   g.Bimg = m->Bimg_fwd;
   g.C = ws.vposed; g.ldc = m->NP; g.split_stride = 0;
-  g.bias = m->vt;
+  g.bias = m->vt; g.terms = 3; g.k_zero_from = -1;
+  if (betas_shared) {
+    // betas are shared by all frames (the fitting loop, optimization.py:196-202): the shape blend is frame independent,
+    // so it is evaluated once in exact fp32 and enters as the bias; the tensor cores see only the pose rows, where the
+    // constant operand's rounded hi half is enough (posedirs offsets are ~1e-2 of a vertex coordinate: the dropped
+    // A.B_lo term is < 1e-6 of it), which also halves the B bytes every tile pulls through L2
+    int rc = launch_vshaped(m, betas_shared, ws, st);
+    if (rc) return rc;
+    g.bias = ws.vshaped; g.terms = 2; g.k_zero_from = m->P;
+  }
   g.NT = 256; g.n_tiles = m->NP / 256; g.m_tiles = (F + BM - 1) / BM;
   g.kb_total = m->KP / BK; g.k_splits = 1; g.kb_per_split = g.kb_total; g.n_valid = m->NP;
   ProfScope ps_("vposed_gemm", st);
@@ -313,7 +366,7 @@ int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStre
   g.A = ws.gvposed; g.lda = m->NP; g.M = F;
   g.Bimg = m->Bimg_bwd;
   g.C = ws.gcoef; g.ldc = m->KP; g.split_stride = (long)F * m->KP;
-  g.bias = nullptr;
+  g.bias = nullptr; g.terms = 3; g.k_zero_from = -1;
   g.NT = m->KP; g.n_tiles = 1; g.m_tiles = (F + BM - 1) / BM;
   g.kb_total = m->NP / BK; g.k_splits = uuo_gcoef_splits(m, F);
   g.kb_per_split = (g.kb_total + g.k_splits - 1) / g.k_splits; g.n_valid = m->KP;
