@@ -372,3 +372,28 @@ def make_lbs_microbench(num_frames: int = 4096, seed: int = 2) -> Dict[str, np.n
         "g_vertices": rng.normal(0, 1, size=(F, NUM_VERTS, 3)).astype(f32),
         "g_joints": rng.normal(0, 1, size=(F, NUM_JOINTS + len(EXTRA_JOINT_VERTEX_IDS), 3)).astype(f32),
     }
+
+
+def make_phalp_like(num_frames: int = 40, seed: int = 17, gaps=((0, 3), (11, 16), (25, 26), (37, 40))) -> Dict:
+    """A PHALP-tracker-shaped per-frame dictionary (the .pkl the reference reads through ImgSmpl,
+    src/video_mocap/img_smpl/img_smpl.py:13-137) with synthetic content: frames inside ``gaps`` carry no track."""
+    rng = np.random.default_rng(seed)
+    aa = _smooth_series(rng, num_frames, (NUM_JOINTS, 3), 0.6)
+    rot = axis_angle_to_matrix_np(aa).astype(np.float32)
+    out = {}
+    for f in range(num_frames):
+        missing = any(a <= f < b for a, b in gaps)
+        j3 = rng.normal(0, 0.5, size=(45, 3)).astype(np.float32) + np.array([0.0, 0.0, 3.0], dtype=np.float32)
+        j2 = (rng.uniform(0.2, 0.8, size=(45, 2)) + 0.001 * f).astype(np.float32)
+        rec = {"tracked_ids": [] if missing else [1], "smpl": [], "3d_joints": [], "2d_joints": [], "camera_bbox": [],
+               "center": [], "scale": [], "size": []}
+        if not missing:
+            rec["smpl"] = [{"global_orient": rot[f, :1], "body_pose": rot[f, 1:], "betas": rng.normal(0, 1, 10).astype(np.float32)}]
+            rec["3d_joints"] = [j3]
+            rec["2d_joints"] = [j2.reshape(-1)]
+            rec["camera_bbox"] = [rng.normal(0, 1, 3).astype(np.float32)]
+            rec["center"] = [rng.uniform(100, 500, 2).astype(np.float32)]
+            rec["scale"] = [np.float32(rng.uniform(100, 300))]
+            rec["size"] = [np.array([720.0, 1280.0], dtype=np.float32)]
+        out["frame_%05d.jpg" % f] = rec
+    return out
