@@ -143,6 +143,18 @@ def main():
         out.update(ch0_loss=np.float32(ev.loss), ch0_g_trans=ev.grads[0].numpy(), ch0_g_z=ev.grads[1].numpy(),
                    ch0_g_betas=ev.grads[2].numpy(), ch0_g_pose=ev.grads[3].numpy())
 
+        # -- optim_chamfer with yaw_lock: False (:167-172, :194, :282-283): the free 3x3 "z_angle" IS the root inside the closure
+        cfg3 = {**cfg, "stages": {**cfg["stages"], "chamfer": {**cfg2["stages"]["chamfer"], "yaw_lock": False}}}
+        pose, betas, root, trans = (T(k) for k in ("ch_pose", "ch_betas", "ch_root", "ch_trans"))
+        for t in (pose, betas, trans):
+            t.requires_grad_(True)
+        z33 = T("mk_root")                       # a slightly non-orthonormal 3x3 per frame to evaluate at
+        OneEvaluation.at = {1: z33}
+        ns["optim_chamfer"](markers, pose, T("ch_o_pose"), betas, T("ch_o_betas"), root, trans, torch.ones(Fn), None, si, cfg3)
+        ev = OneEvaluation.last
+        out.update(ch3_z=z33.numpy(), ch3_loss=np.float32(ev.loss), ch3_g_trans=ev.grads[0].numpy(), ch3_g_z=ev.grads[1].numpy(),
+                   ch3_g_betas=ev.grads[2].numpy(), ch3_g_pose=ev.grads[3].numpy(), ch3_root_baked=root.detach().numpy())
+
         # -- compute_nearest_points (optimization.py:402-642), use_mean branch, one frame masked out
         OneEvaluation.at = None
         img_mask = torch.ones(Fn)
@@ -155,6 +167,30 @@ def main():
         out["np_img_mask"] = img_mask.numpy()
         out["np_vertex_idx"] = torch.argmax(one_hot, dim=1).numpy()
         assert float(one_hot.sum()) == M
+        # the use_mean: False branch (per-frame closest_point, :503-510, 538-590) for the three granularities
+        cfg_cp = {**cfg, "stages": {**cfg["stages"], "compute_locations": {"use_velocity": False, "use_barycentric": False,
+                                                                          "use_mean": False}}}
+        mask2 = torch.ones(Fn)
+        mask2[Fn - 1] = 0                                     # the last frame carries no video prior
+        lab = np.random.default_rng(9).integers(0, 24, size=(Fn, M))
+        lab[Fn - 2, ::3] = 23                                 # label 23 is outside range(num_joints = 23): not updated there
+        out["cp_img_mask"], out["cp_labels"] = mask2.numpy(), lab
+        with torch.no_grad():
+            vv = si(poses=p3d.normalize_rot(T("ch_pose")), betas=T("ch_betas").repeat(Fn, 1),
+                    root_orient=p3d.normalize_rot(T("mk_root")), trans=T("ch_trans"))["vertices"].numpy()
+        for gran in ("full", "marker", "part"):
+            oh = ns["compute_nearest_points"](
+                markers=markers, pose_body=T("ch_pose"), betas=T("ch_betas"), root_orient=T("mk_root"), trans=T("ch_trans"),
+                smpl_inference=si, marker_labels=lab, granularity=gran, img_mask=mask2, device=torch.device("cpu"),
+                config=cfg_cp, o_pose_body=None, window_size=1, use_velocity=False)
+            # the reference scatters the weight 1 and then the two zero weights to the SAME index (:543-549), so this branch
+            # returns an all-zero matrix; what it computed before that is closest_point of the last frame that updates a row
+            assert float(oh.abs().sum()) == 0.0, gran
+            want = np.zeros(M, dtype=np.int64)
+            for c in range(M):
+                fr = [f for f in range(Fn) if mask2[f] == 1 and (gran != "part" or lab[f, c] < 23)]
+                want[c] = ns["closest_point"](markers[fr[-1]].numpy(), vv[fr[-1]])["vertex_indices"][c]
+            out["cp_idx_" + gran] = want
 
         # -- optim_markers (optimization.py:288-399): params = [pose_body, betas, root_orient, trans]
         vidx = torch.from_numpy(g["mk_vidx"]).long()

@@ -325,3 +325,46 @@ def test_marker_labels_from_coords_and_weighted_mse(ctx):
         assert lab.shape == (7, 5) and torch.equal(lab.cpu(), want.unsqueeze(0).expand(7, 5))
     a, b, w = torch.randn(4, 3, device="cuda:0"), torch.randn(4, 3, device="cuda:0"), torch.rand(4, 3, device="cuda:0")
     assert torch.allclose(weighted_mse_loss(a, b, w), (((a - b) ** 2) * w).mean())
+
+
+def test_chamfer_closure_free_root_matches_reference_source(ctx, golden):
+    """``yaw_lock: False`` (optimization.py:167-172, 194, 282-283): the free 3x3 per frame IS the root orientation inside
+    the closure; loss, every gradient and the baked root against the reference's own function run from source."""
+    from uuo_mocap_b200 import fit
+    from uuo_mocap_b200.fit import FitProblem, ParamBlock, chamfer_closure
+    _, smpl, _ = ctx
+    g, r = golden("closure_top4.npz"), golden("closure_ref.npz")
+    prob = FitProblem(smpl, _T(g["markers"]), _T(g["ch_o_pose"]), _T(g["ch_o_betas"]))
+    pb = ParamBlock.build({"trans": _T(g["ch_trans"]), "z_angle": _T(r["ch3_z"]), "betas": _T(g["ch_betas"]),
+                           "pose_body": _T(g["ch_pose"])}, "cuda:0")
+    loss = chamfer_closure(prob, pb, _T(g["ch_root"]).cuda(), {"full_chamfer": 10.0, "reg_pose_body": 1.0, "reg_betas": 1.0})
+    assert abs(float(loss) - float(r["ch3_loss"])) <= 1e-5 * abs(float(r["ch3_loss"]))
+    for k, ref in (("pose_body", "ch3_g_pose"), ("betas", "ch3_g_betas"), ("trans", "ch3_g_trans"), ("z_angle", "ch3_g_z")):
+        assert rel_err(pb.gviews[k].cpu().numpy().reshape(r[ref].shape), r[ref]) < 1e-4, k
+    baked = (fit.normalize_rot(_T(r["ch3_z"]).cuda()) @ _T(g["ch_root"]).cuda()).cpu().numpy()
+    assert rel_err(baked, r["ch3_root_baked"]) < 1e-6
+    # through the stage function: zero iterations leave the identity offset, so root_orient comes back unchanged
+    cfg = fit.default_config(num_iters=0, optimizer="adam")
+    cfg["stages"]["chamfer"]["yaw_lock"] = False
+    root = _T(g["ch_root"]).cuda()
+    fit.optim_chamfer(_T(g["markers"]), _T(g["ch_pose"]).cuda(), _T(g["ch_o_pose"]), _T(g["ch_betas"]).cuda(),
+                      _T(g["ch_o_betas"]), root, _T(g["ch_trans"]).cuda(), None, None, smpl, cfg)
+    assert rel_err(root.cpu().numpy(), g["ch_root"]) < 1e-6
+
+
+@pytest.mark.parametrize("gran", ["full", "marker", "part"])
+def test_compute_nearest_points_closest_point_branch(ctx, golden, gran):
+    """compute_locations.use_mean: False (optimization.py:503-510, 538-590): per-frame closest_point; the last frame that
+    updates a marker's row wins.  Expected indices = the reference's own closest_point (utils/points.py:19-42) on that
+    frame (the reference's matrix itself comes out all zero there: its scatter_ calls overwrite the 1, see the generator)."""
+    from uuo_mocap_b200 import fit
+    _, smpl, _ = ctx
+    g, r = golden("closure_top4.npz"), golden("closure_ref.npz")
+    cfg = fit.default_config()
+    cfg["stages"]["compute_locations"] = {"use_velocity": False, "use_barycentric": False, "use_mean": False}
+    mk, pose, betas, root, trans = (_T(g[k]) for k in ("markers", "ch_pose", "ch_betas", "mk_root", "ch_trans"))
+    idx = fit.compute_nearest_points(mk, pose.cuda(), betas.cuda(), root.cuda(), trans.cuda(), smpl,
+                                     marker_labels=_T(r["cp_labels"]), granularity=gran, img_mask=_T(r["cp_img_mask"]),
+                                     config=cfg, as_one_hot=False).cpu().numpy()
+    want = r["cp_idx_" + gran]
+    assert (idx == want).mean() > 0.95          # vertices differ from the reference's by ~1e-7: a near-tie may flip

@@ -176,14 +176,18 @@ class ParamBlock:
 
 def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor, losses: Dict[str, float]) -> torch.Tensor:
     """closure_stage_chamfer (optimization.py:187-258): fills pb.grad, returns the loss (device scalar).
-    Parameters: trans [F,3], z_angle [F], betas [G,10], pose_body [F,23,3,3]; root_orient is constant."""
+    Parameters: trans [F,3], z_angle, betas [G,10], pose_body [F,23,3,3]; root_orient is constant.
+    ``z_angle`` [F] is the yaw of ``yaw_lock: True`` (:192, root = Rz(z) @ root_orient); a [F,1,3,3] ``z_angle`` is the
+    free 3x3 of ``yaw_lock: False`` (:194), which the reference uses AS the root orientation inside the closure."""
     v, g = pb.views, pb.gviews
     F, M, Fg = prob.F, prob.M, prob.F_global
     pb.grad.zero_()
     prob.red.zero_()
     brows = prob.betas_rows(v["betas"])
+    free_root = v["z_angle"].dim() == 4
+    root_in, yaw_in = (v["z_angle"], None) if free_root else (root_orient, v["z_angle"])
     with torch.cuda.device(prob.dev):
-        verts = prob.lbs_forward(brows, root_orient, v["pose_body"], v["z_angle"], v["trans"])
+        verts = prob.lbs_forward(brows, root_in, v["pose_body"], yaw_in, v["trans"])
         w_ch = float(losses.get("full_chamfer", 0.0))
         if w_ch != 0.0 and prob.wsum_global > 0:
             # dropped markers (mask 0) weigh nothing in the loss or the gradient: the kernel does not search them;
@@ -198,8 +202,9 @@ def chamfer_closure(prob: FitProblem, pb: ParamBlock, root_orient: torch.Tensor,
             prob.g_rows.zero_()
             prob.idx.zero_()
             prob.pos.zero_()
-        prob.lbs_backward_rows(brows, root_orient, v["pose_body"], v["z_angle"], prob.idx, False, prob.g_rows,
-                               prob.gbetas_target(), None, g["pose_body"], g["z_angle"], g["trans"], cached_pos=prob.pos)
+        prob.lbs_backward_rows(brows, root_in, v["pose_body"], yaw_in, prob.idx, False, prob.g_rows,
+                               prob.gbetas_target(), g["z_angle"] if free_root else None, g["pose_body"],
+                               None if free_root else g["z_angle"], g["trans"], cached_pos=prob.pos)
         if "reg_pose_body" in losses:                                                   # :243-245
             prob.sqdiff(v["pose_body"], prob.o_pose_body, losses["reg_pose_body"] / (Fg * v["pose_body"][0].numel()),
                         g["pose_body"])
@@ -415,13 +420,14 @@ def optim_chamfer(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
     """optimization.py:147-285.  Updates trans, betas, pose_body and root_orient IN PLACE like the reference
     (its parameters are leaf tensors stepped by the optimiser; root_orient gets the fitted yaw baked in)."""
     st = config["stages"]["chamfer"]
-    if not st.get("yaw_lock", True):
-        raise NotImplementedError("yaw_lock: False (free 3x3 root offset) is not on the CUDA path")
+    yaw_lock = bool(st.get("yaw_lock", True))
     prob = problem or FitProblem(smpl_inference, markers, o_pose_body, o_betas, shard, groups)
     F = prob.F
     dev = prob.dev
     root = root_orient.detach().to(dev, torch.float32).contiguous()
-    pb = ParamBlock.build({"trans": trans, "z_angle": torch.zeros(F, device=dev), "betas": betas.reshape(-1, prob.mh.NB),
+    # :165-172: a yaw angle per frame, or (yaw_lock: False) a free 3x3 per frame that starts at the identity
+    z0 = torch.zeros(F, device=dev) if yaw_lock else torch.eye(3, device=dev).expand(F, 1, 3, 3).contiguous()
+    pb = ParamBlock.build({"trans": trans, "z_angle": z0, "betas": betas.reshape(-1, prob.mh.NB),
                            "pose_body": pose_body}, dev)
     losses = dict(st["losses"])
     closure = lambda: chamfer_closure(prob, pb, root, losses)
@@ -435,7 +441,10 @@ def optim_chamfer(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
         trans.copy_(pb.views["trans"])
         betas.copy_(pb.views["betas"].view_as(betas))
         pose_body.copy_(pb.views["pose_body"])
-        root_orient.copy_(rot_z(pb.views["z_angle"].view(F, 1, 1)) @ root)          # :280-285
+        if yaw_lock:
+            root_orient.copy_(rot_z(pb.views["z_angle"].view(F, 1, 1)) @ root)      # :280-281
+        else:
+            root_orient.copy_(normalize_rot(pb.views["z_angle"]) @ root)            # :282-283
     return prob
 
 
@@ -476,13 +485,16 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
                            granularity: str = "full", img_mask=None, device=None, config: Optional[Dict] = None,
                            o_pose_body=None, window_size: int = 1, use_velocity: bool = True,
                            shard: Optional[Shard] = None, as_one_hot: bool = True):
-    """optimization.py:402-642, the shipped ``use_mean: True`` branch (:422-430,464-486,595-603): SMPL forward
-    with the mean betas, mean over the frames with img_mask == 1 of the marker-vertex distances, argmin.
+    """optimization.py:402-642.  The shipped ``use_mean: True`` branch (:422-430,464-486,595-603): SMPL forward with the
+    mean betas, mean over the frames with img_mask == 1 of the marker-vertex distances, argmin.  ``use_mean: False``:
+    per-frame ``closest_point`` (see ``_closest_point_last_frames``).  ``use_barycentric`` (igl / trimesh) is not taken.
     Returns the [M,V] one-hot matrix like the reference (or the index vector)."""
+    use_mean = True
     if config is not None:
         cl = config["stages"].get("compute_locations", {})
-        if not cl.get("use_mean", True) or cl.get("use_barycentric", False):
-            raise NotImplementedError("only compute_locations.use_mean (the shipped setting) is on the CUDA path")
+        if cl.get("use_barycentric", False):
+            raise NotImplementedError("compute_locations.use_barycentric needs igl / trimesh (not on the CUDA path)")
+        use_mean = bool(cl.get("use_mean", True))
     smpl = _model_of(smpl_inference)
     mh = smpl.handle
     dev = mh.device
@@ -498,17 +510,63 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
     with torch.cuda.device(dev):
         check(_lib.lib().uuo_lbs_forward(mh.handle, ptr(mean_betas), 1, ptr(root), ptr(pose), POSE_RAW6D, None, ptr(tr), F,
                                          ptr(vertices), None, ptr(ws), stream_ptr(dev)))
-    fm = img_mask.to(dev, torch.float32).contiguous() if img_mask is not None else None
-    _, acc = ops.mean_distance_argmin(mk, vertices, fm, finalize=False)
-    cnt = torch.tensor([float(F if fm is None else (fm == 1).sum().item())], dtype=torch.float64)
-    cnt = shard.all_reduce_sum(cnt)
-    shard.all_reduce_sum_(acc)                                                       # [M,V] fp32, once per stage
-    idx = ops.mean_argmin(acc, max(float(cnt.item()), 1.0))
+    fm = img_mask.to(dev, torch.float32).reshape(-1).contiguous() if img_mask is not None else None
+    if fm is not None and fm.numel() != F:
+        raise ValueError("img_mask must hold one entry per frame (%d), got %d" % (F, fm.numel()))
+    if use_mean:
+        _, acc = ops.mean_distance_argmin(mk, vertices, fm, finalize=False)
+        cnt = torch.tensor([float(F if fm is None else (fm == 1).sum().item())], dtype=torch.float64)
+        cnt = shard.all_reduce_sum(cnt)
+        shard.all_reduce_sum_(acc)                                                   # [M,V] fp32, once per stage
+        idx = ops.mean_argmin(acc, max(float(cnt.item()), 1.0))
+    else:
+        idx = _closest_point_last_frames(mk, vertices, fm, marker_labels, granularity, pose.shape[1], shard)
     if not as_one_hot:
         return idx
     one_hot = torch.zeros((M, mh.V), dtype=torch.float32, device=dev)                # :601-603
     one_hot[torch.arange(M, device=dev), idx.long()] = 1.0
     return one_hot
+
+
+def _closest_point_last_frames(mk, vertices, fm, marker_labels, granularity, num_joints, shard):
+    """The ``use_mean: False`` branch of compute_nearest_points (optimization.py:503-510, 538-590) as the reference runs
+    it (window_size = 1): every valid frame is its own window whose running minimum starts at infinity, so each frame's
+    per-frame ``closest_point`` result (utils/points.py:19-42: argmin over vertices of the UN-squared distance)
+    overwrites the previous one -- the output is the correspondence of the LAST frame with img_mask == 1 ("full" and
+    "marker" granularity), or per marker column the last valid frame in which its label is one of the body joints
+    ("part").  The frame's [M,V] distance matrix comes from the mean-distance kernel run on that one frame (same op
+    order as np.linalg.norm, first minimum wins)."""
+    F, M = mk.shape[:2]
+    dev = mk.device
+    valid = torch.ones(F, dtype=torch.bool, device=dev) if fm is None else fm == 1
+    if granularity == "part":
+        if marker_labels is None:
+            raise ValueError("granularity 'part' needs marker_labels [F,M]")
+        lab = torch.as_tensor(marker_labels).to(dev)
+        ok = valid.view(F, 1) & (lab >= 0) & (lab < num_joints)
+    else:
+        ok = valid.view(F, 1).expand(F, M)
+    fr = torch.arange(F, device=dev).view(F, 1).expand(F, M)
+    last = torch.where(ok, fr, torch.full_like(fr, -1)).max(dim=0)[0]                 # [M] local frame, -1 = none
+    # frame-range shards: the globally last frame wins; its owner contributes the indices
+    offset = 0
+    if shard.world > 1:
+        sizes = torch.zeros(shard.world, dtype=torch.float64)
+        sizes[shard.rank] = F
+        sizes = shard.all_reduce_sum(sizes)
+        offset = int(sizes[:shard.rank].sum().item())
+    glast = torch.where(last >= 0, last + offset, last).to(torch.float32)
+    gmax = glast.clone()
+    if shard.world > 1:
+        torch.distributed.all_reduce(gmax, op=torch.distributed.ReduceOp.MAX, group=shard.group)
+    idx = torch.zeros(M, dtype=torch.float32, device=dev)
+    mine = (glast == gmax) & (last >= 0)
+    for f in torch.unique(last[mine]).tolist():
+        cols = mine & (last == f)
+        vi, _ = ops.mean_distance_argmin(mk[f:f + 1].contiguous(), vertices[f:f + 1].contiguous())
+        idx = torch.where(cols, vi.to(torch.float32), idx)
+    shard.all_reduce_sum_(idx)
+    return idx.to(torch.int32)
 
 
 def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient, trans, img_mask, smpl_inference,
