@@ -466,15 +466,26 @@ def run_fit(args, rank, world, local, dev, light=False):
     sampler = ClockSampler(local) if rank == 0 else None
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
-    # ---- pass 1 (eager, the library's per-kernel events on): the kernel breakdown behind `roofline`
-    ops.profile_enable(True)
-    p0, p1, p2 = ev(), ev(), ev()
-    barrier()
-    p0.record(); run_n("ch", n_ch, False); p1.record(); run_n("mk", n_mk, False); p2.record()
-    barrier()
-    prof = ops.profile_read()
-    ops.profile_enable(False)
-    prof_ms = p0.elapsed_time(p2)
+    # ---- pass 1 (eager, the library's per-kernel events on, one stage after the other): the per-iteration kernel times
+    # behind `roofline` (a kernel may be launched several times per iteration, e.g. once per frame chunk: times are summed)
+    def profiled(stage, n):
+        ops.profile_enable(True)
+        a, b = ev(), ev()
+        barrier()
+        a.record(); run_n(stage, n, False); b.record()
+        barrier()
+        pr = ops.profile_read()
+        ops.profile_enable(False)
+        return {k: (v[0] / max(n, 1), v[1] / max(n, 1)) for k, v in (pr or {}).items()}, a.elapsed_time(b)
+    prof_ch, pms_ch = profiled("ch", n_ch)
+    prof_mk, pms_mk = profiled("mk", n_mk)
+    prof_ms = pms_ch + pms_mk
+    # ms per step-pair of stages summed per kernel, launches per iteration
+    prof = {}
+    for pr, n in ((prof_ch, n_ch), (prof_mk, n_mk)):
+        for k, (ms_it, cnt_it) in pr.items():
+            t, c = prof.get(k, (0.0, 0.0))
+            prof[k] = (t + ms_it * n, c + cnt_it * n)
 
     # ---- pass 2 (the timed K steps): one captured iteration per stage replayed (eager when graphs are off)
     if use_graph:
@@ -500,12 +511,13 @@ def run_fit(args, rank, world, local, dev, light=False):
                 "marker": {"iters": n_mk, "ms_per_iter": ms_mk / max(n_mk, 1),
                            "frame_iters_per_sec": frames_global * n_mk / (ms_mk * 1e-3) if n_mk else None}}
 
-    kern = {k: round(v[0] / max(v[1], 1), 4) for k, v in (prof or {}).items()}
+    kern = {"chamfer_iteration": {k: round(v[0], 4) for k, v in prof_ch.items()},
+            "marker_iteration": {k: round(v[0], 4) for k, v in prof_mk.items()}}
     if light:
         if sampler:
             sampler.stop()
         return {"value": value, "unit": UNIT, "ms_per_step": ms_all / K, "steps": K, "frames_this_rank": F,
-                "stages": stage_rates(), "ms_per_launch": kern, "cuda_graph": bool(use_graph)}
+                "stages": stage_rates(), "ms_per_kernel": kern, "cuda_graph": bool(use_graph)}
 
     # ---- e2e: the reference's stage functions with HOST tensors in and out (optim_chamfer -> compute_nearest_points
     # -> optim_markers), the same n_ch / n_mk Adam iterations, copies inside the timed region
@@ -573,12 +585,14 @@ def run_fit(args, rank, world, local, dev, light=False):
         roofline = None
         if prof:
             dom = max(prof.items(), key=lambda kv: kv[1][0])[0]
-            roofline = {"kernel": dom, "share_of_step": prof[dom][0] / prof_ms, "launches": prof[dom][1],
-                        "ms_per_launch": kern, "traffic": None}
+            roofline = {"kernel": dom, "share_of_step": prof[dom][0] / prof_ms, "launches": int(round(prof[dom][1])),
+                        "ms_per_kernel": kern, "traffic": None,
+                        "note": "ms_per_kernel = device time of the kernel per ITERATION of the stage (all its launches summed)"}
             table = {}
             for k, (bound, work) in algo.items():
-                if k in prof and prof[k][1] > 0:
-                    dur = prof[k][0] / prof[k][1] * 1e-3
+                per_it = (prof_ch.get(k) or prof_mk.get(k))       # time per iteration over this rank's F frames
+                if per_it and per_it[0] > 0:
+                    dur = per_it[0] * 1e-3
                     if bound == "hbm":
                         ach, peak, unit = work / dur / 1e9, peaks["hbm"], "GB/s"
                     else:
@@ -586,7 +600,7 @@ def run_fit(args, rank, world, local, dev, light=False):
                     table[k] = {"bound": bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak}
             if dom in table:
                 roofline.update(table[dom])
-                roofline["peak_source"] = peaks["src"] + (" (TF32 dense = bf16/2; logical flops, the 3xTF32 split issues 3x)"
+                roofline["peak_source"] = peaks["src"] + (" (TF32 dense = bf16/2; logical flops, the split issues 2-3 MMAs per product)"
                                                           if table[dom]["bound"] == "tensor" else "")
                 # ncu captures of the fit kernels were taken at F = 5000 per launch
                 roofline["traffic"] = traffic.get(dom) if F == 5000 and dom in FIT_TRAFFIC_KEYS else None
@@ -606,7 +620,7 @@ def run_fit(args, rank, world, local, dev, light=False):
                               "off), frame chunks of 256", "chamfer_s": r["chamfer_s"], "marker_s": r["marker_s"]}
             except Exception as e:
                 tg = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:160])}
-        launches = int(sum(v[1] for v in (prof or {}).values()))
+        launches = int(round(sum(v[1] for v in (prof or {}).values())))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
             "ms_per_step": ms_all / K, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,

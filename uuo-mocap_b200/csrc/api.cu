@@ -22,7 +22,12 @@ extern "C" int uuo_lbs_forward(const uuo_model* m, const float* betas, int betas
   cudaStream_t st = (cudaStream_t)stream;
   uuo_ws ws = carve_ws(m, F, workspace);
   if ((rc = launch_fk_forward(m, betas, betas_rows, global_orient, body_pose, pose_mode, yaw, transl, F, joints, ws, st))) return rc;
-  if ((rc = launch_vposed_gemm(m, F, ws, betas_rows == 1 ? betas : nullptr, st))) return rc;
+  const bool shared = betas_rows == 1;
+  if (shared && (rc = launch_vshaped(m, betas, ws, st))) return rc;
+  // (r2: running GEMM -> skinning in 1024-frame chunks so that v_posed is read back from L2 was measured and lost:
+  // vposed_gemm 0.187 -> 0.289 ms, skin_forward 0.176 -> 0.225 ms at F = 5000 -- the persistent kernels' tails
+  // (648 items over 148 SMs per chunk) cost more than the HBM read saves)
+  if ((rc = launch_vposed_gemm(m, F, ws, shared, st))) return rc;
   if ((rc = launch_skin_forward(m, transl, F, vertices, joints, ws, st))) return rc;
   return UUO_OK;
 }

@@ -166,10 +166,11 @@ int launch_fk_backward(const uuo_model* m, const float* betas, int betas_rows, c
 void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int K, int NT);
 // betas_shared != NULL: ONE betas row for all frames -> v_shaped is evaluated once in exact fp32 (launch_vshaped) and
 // only the pose rows go through the tensor cores
-int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st);
+// (launch_vshaped must have filled ws.vshaped when betas_shared is set)
+int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, bool betas_shared, cudaStream_t st);
 int launch_vshaped(const uuo_model* m, const float* betas, const uuo_ws& ws, cudaStream_t st);
 int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st);
-int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st);
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, bool betas_shared, cudaStream_t st);
 int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int uuo_gcoef_splits(const uuo_model* m, int F);
 int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);

@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(256) sgemm_kernel(const float* __restrict__ Am
 // The release library has ONE GEMM path (tcgen05).  A build with -DUUO_DEBUG_SIMT keeps the SIMT kernels above and
 // lets UUO_GEMM_SIMT=1 select them per call (debug cross-check of the tensor-core path).
 #ifndef UUO_DEBUG_SIMT
-int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st) {
+int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, bool betas_shared, cudaStream_t st) {
   return launch_vposed_gemm_umma(m, F, ws, betas_shared, st);
 }
 int launch_gcoef_gemm(const uuo_model* m, int F, const uuo_ws& ws, int* n_parts, cudaStream_t st) {
@@ -144,7 +144,7 @@ static bool use_simt() {
   return e && e[0] == '1';
 }
 
-int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st) {
+int launch_vposed_gemm(const uuo_model* m, int F, const uuo_ws& ws, bool betas_shared, cudaStream_t st) {
   if (!use_simt()) return launch_vposed_gemm_umma(m, F, ws, betas_shared, st);
   // M = F, K = KP, N = NP (padded columns are zeros in Bmat and vt)
   dim3 grid(m->NP / 128, (F + 127) / 128, 1);

@@ -340,7 +340,7 @@ int launch_vshaped(const uuo_model* m, const float* betas, const uuo_ws& ws, cud
   return UUO_OK;
 }
 
-int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, const float* betas_shared, cudaStream_t st) {
+int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, bool betas_shared, cudaStream_t st) {
   GemmArgs g;
   g.A = ws.coef; g.lda = m->KP; g.M = F;
   g.Bimg = m->Bimg_fwd;
@@ -351,8 +351,6 @@ int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, const f
     // so it is evaluated once in exact fp32 and enters as the bias; the tensor cores see only the pose rows, where the
     // constant operand's rounded hi half is enough (posedirs offsets are ~1e-2 of a vertex coordinate: the dropped
     // A.B_lo term is < 1e-6 of it), which also halves the B bytes every tile pulls through L2
-    int rc = launch_vshaped(m, betas_shared, ws, st);
-    if (rc) return rc;
     g.bias = ws.vshaped; g.terms = 2; g.k_zero_from = m->P;
   }
   g.NT = 256; g.n_tiles = m->NP / 256; g.m_tiles = (F + BM - 1) / BM;
