@@ -185,6 +185,11 @@ int uuo_sqdiff_accumulate(const float* x, const float* y, size_t n, float scale,
 int uuo_temporal_accumulate(const float* x, const float* prev2, const float* next2, int F, int D, float scale,
                             float* loss_sum, float* g, void* stream);
 /* mm[F,3] = mean over ALL M markers of the frame (optimization.py:248; dropped markers included). */
+/* Part fits (src/video_mocap/markers/markers_utils.py:441-444, 463: chamfer against vertices[:, vertex_indices] of one
+ * candidate sub-tree): G candidates are stacked along the frame axis, frames_per_group frames each; keep[G][V] (uint8, row
+ * numbering of `vertices`) marks a candidate's vertex subset.  Rows that are not kept are overwritten with far_value, so
+ * the nearest-vertex kernels, run over the whole array, return the nearest KEPT vertex. */
+int uuo_mask_vertices(float* vertices, const uint8_t* keep, int F, int V, int frames_per_group, float far_value, void* stream);
 int uuo_marker_mean(const float* markers, int F, int M, float* mm, void* stream);
 /* "trans_vel" (optimization.py:246-250): mse(trans[1:]-trans[:-1], mm[1:]-mm[:-1]).  prev[6] / next[6] =
  * [trans(3), mm(3)] of the frame before row 0 / after row F-1 (NULL at the ends of the sequence). */

@@ -220,3 +220,41 @@ def test_part_fits_match_reference_source(ctx, golden):
     assert rel_err(out["aabb_volume_ratio"].cpu().numpy(), r["pfB_aabb"]) < 1e-6
     assert rel_err(out["trans"].cpu().numpy(), r["pfB_trans"]) < 1e-6
     assert rel_err(out["root_orient"].cpu().numpy(), r["pfB_root"]) < 1e-6
+
+
+def test_batched_part_fits_equal_sequential_adam(ctx):
+    """the candidates of find_best_part_fits as hypothesis groups of ONE stacked problem
+    (fit_subtrees_batched: fused Adam, CUDA-graph replay) against the same candidates fitted one after the other with
+    torch.optim.Adam over the autograd path (fit_subtrees): same parameters after a fixed iteration count, same scores,
+    same ranking, same output dict."""
+    from uuo_mocap_b200 import parts, synthetic
+    model, smpl, _ = ctx
+    F, iters = 8, 25
+    cap, rot = _case(model, F=F, seed=23)
+    vlab = np.argmax(model.weights, axis=-1)
+    rng = np.random.default_rng(5)
+    vids = np.concatenate([rng.choice(np.where(vlab == j)[0], size=6, replace=False) for j in (16, 18, 20)])
+    verts = synthetic.lbs_numpy(model, cap.gt_betas, rot.astype(np.float64), cap.gt_trans.astype(np.float64), vertex_ids=vids)
+    markers = _T(verts.astype(np.float32))
+    markers[2, 3] = 0.0                                   # a dropped marker counts like any other here (unweighted chamfer)
+    labels = torch.from_numpy(np.repeat(vlab[vids][None], F, 0).astype(np.int64))
+    cfg = {"optimizer": {"name": "adam", "lr": 0.01},
+           "stages": {"part": {"mode": "cluster", "num_iters": iters, "losses": {"chamfer": 10.0, "reg_betas": 0.1}}}}
+    cands = [[16, 18, 20], [17, 19, 21], [1, 4, 7], [0, 1, 2]]
+    r = _T(rot)
+    b0 = _T(cap.gt_betas * 0.5)
+    seq = parts.fit_subtrees(markers, r[:, 1:], b0, r[:, :1], smpl, cands, cfg)
+    bat = parts.fit_subtrees_batched(markers, r[:, 1:], b0, r[:, :1], smpl, cands, cfg)
+    for a, b in zip(seq, bat):
+        assert a["subtree"] == b["subtree"]
+        assert rel_err(b["trans"].cpu().numpy(), a["trans"].cpu().numpy()) < 1e-4
+        assert rel_err(b["betas"].cpu().numpy(), a["betas"].cpu().numpy()) < 1e-3
+        assert abs(float(b["z_angle"]) - float(a["z_angle"])) < 1e-4
+        assert abs(b["distance"] - a["distance"]) <= 1e-3 * abs(a["distance"])
+    # a two-candidate chunking gives the same fits (groups are independent)
+    bat2 = parts.fit_subtrees_batched(markers, r[:, 1:], b0, r[:, :1], smpl, cands, cfg, max_groups=2)
+    for a, b in zip(bat, bat2):
+        assert rel_err(b["trans"].cpu().numpy(), a["trans"].cpu().numpy()) < 1e-5
+    out = parts.find_best_part_fits(markers, r[:, 1:], b0, r[:, :1], labels, smpl, model.parents, cfg, subtrees=cands)
+    assert [s for s, _ in out["ranking"]] == [f["subtree"] for f in sorted(seq, key=lambda f: f["distance"])]
+    assert out["chain"].tolist() == out["ranking"][0][0]

@@ -43,6 +43,7 @@ SIGNATURES = {
     "uuo_mean_argmin": (_I, [_P, _I, _I, _F, _P, _P]),
     "uuo_sqdiff_accumulate": (_I, [_P, _P, _SZ, _F, _P, _P, _P]),
     "uuo_temporal_accumulate": (_I, [_P, _P, _P, _I, _I, _F, _P, _P, _P]),
+    "uuo_mask_vertices": (_I, [_P, _P, _I, _I, _I, _F, _P]),
     "uuo_marker_mean": (_I, [_P, _I, _I, _P, _P]),
     "uuo_transvel_accumulate": (_I, [_P, _P, _P, _P, _I, _F, _P, _P, _P]),
     "uuo_point_error_mean": (_I, [_P, _P, _I, _I, _P, _I, _I, _F, _P, _P, _P]),

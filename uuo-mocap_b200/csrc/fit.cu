@@ -202,6 +202,33 @@ static inline int nblocks(size_t n) {
   return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
+// rows of `vertices` that the frame's group does not keep are moved far away, so a nearest-vertex search over the
+// whole array behaves like a search over the group's vertex subset (markers_utils.py:441-444, 463: vertices[:, vertex_indices])
+__global__ void __launch_bounds__(256) mask_vertices_kernel(float* __restrict__ vertices, const uint8_t* __restrict__ keep,
+                                                            size_t n, int V, int frames_per_group, float far_value) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const size_t f = i / V;
+  const int row = (int)(i - f * V);
+  if (!keep[(f / frames_per_group) * V + row]) {
+    float* p = vertices + i * 3;
+    p[0] = far_value; p[1] = far_value; p[2] = far_value;
+  }
+}
+
+extern "C" int uuo_mask_vertices(float* vertices, const uint8_t* keep, int F, int V, int frames_per_group, float far_value,
+                                 void* stream) {
+  UUO_CHECK_ARG(vertices && keep && V > 0 && frames_per_group > 0, "bad arguments");
+  UUO_CHECK_ARG(F % frames_per_group == 0, "F must be a multiple of frames_per_group");
+  if (F == 0) return UUO_OK;
+  const size_t n = (size_t)F * V;
+  ProfScope ps_("mask_vertices", (cudaStream_t)stream);
+  mask_vertices_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(vertices, keep, n, V, frames_per_group,
+                                                                                     far_value);
+  UUO_LAUNCH_CHECK();
+  return UUO_OK;
+}
+
 extern "C" int uuo_marker_mask(const float* markers, int n, float* mask, void* stream) {
   UUO_CHECK_ARG(markers && mask && n >= 0, "bad arguments");
   if (n == 0) return UUO_OK;

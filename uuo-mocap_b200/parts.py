@@ -6,10 +6,15 @@ For every candidate sub-tree of the skeleton the reference fits a yaw angle [1,1
 (:454-562: ``10 * chamfer(markers_subset -> vertices_subset) + reg_betas * mse(betas, o_betas)``), scores the fit
 with the bidirectional chamfer distance (:566-579) and labels the markers from the best one (:581-597).
 
-Here every closure evaluation is the dense CUDA lbs() forward/backward (``SMPL.forward`` is an autograd function
-over uuo_lbs_forward/backward) plus the CUDA nearest-neighbour kernel (``losses.chamfer_distance``); the optimiser
-is torch's L-BFGS like the reference, or Adam.  Sub-trees are independent fits; they run one after the other on
-the same device buffers.  Out of scope: the "reproject"/foot/ground terms (they need the HMR camera inputs).
+Two drivers.  ``fit_subtrees`` follows the reference candidate by candidate: every closure evaluation is the dense
+CUDA lbs() forward/backward (``SMPL.forward`` is an autograd function over uuo_lbs_forward/backward) plus the CUDA
+nearest-neighbour kernel (``losses.chamfer_distance``) under torch's L-BFGS (the reference's optimiser; each candidate
+keeps its own line search).  ``fit_subtrees_batched`` (optimizer.name = "adam") fits ALL
+candidates at once: the candidates are independent fits, so they become hypothesis groups stacked along the frame
+axis of ONE problem on the kernels of the fitting loop -- dense forward on the visiting-order twin, the vertices a
+candidate does not own moved away (uuo_mask_vertices), the box-pruned correspondence kernel with last iteration's
+matches as hint, the row-sparse backward, one fused Adam step over every candidate's parameters, the whole
+iteration replayed from a CUDA graph.  Out of scope: the "reproject"/foot/ground terms (they need the HMR camera).
 """
 from __future__ import annotations
 
@@ -18,9 +23,11 @@ from typing import Callable, Dict, List, Optional, Sequence
 import numpy as np
 import torch
 
-from . import ops
-from .fit import _model_of, rot_z
+from . import _lib, ops
+from ._lib import check, ptr
+from .fit import FitProblem, ParamBlock, _model_of, rot_z, run_adam
 from .losses import chamfer_distance
+from .smpl import POSE_ROTMAT
 
 
 def sub_hierarchies(parents, num_bones: int) -> List[List[int]]:
@@ -136,6 +143,94 @@ def fit_subtrees(markers_subset: torch.Tensor, pose_body: torch.Tensor, o_betas:
     return results
 
 
+def fit_subtrees_batched(markers_subset: torch.Tensor, pose_body: torch.Tensor, o_betas: torch.Tensor,
+                         root_orient: torch.Tensor, smpl_inference, subtrees: Sequence[Sequence[int]], config: Dict,
+                         max_groups: int = 64) -> List[Dict]:
+    """All candidate sub-trees of markers_utils.py:413-600 fitted TOGETHER with the fused Adam optimiser: candidate g is
+    hypothesis group g of one stacked problem of G x F frames.  Parameters per candidate as in the reference (:416-418):
+    z_angle [1] (one yaw for the whole sequence), trans [F,3] (starts at the per-frame marker median), betas [1,10];
+    loss per candidate = chamfer * mean_f mean_m min_{v in subset} |m - v|^2 + reg_betas * mse(betas, o_betas)
+    (:463-476, 516-517; unweighted: a marker at the origin counts like any other).  Returns the dicts of
+    ``fit_subtrees`` (the ranking distance is evaluated per candidate after the fit)."""
+    smpl = _model_of(smpl_inference)
+    dev = smpl.device
+    st = config["stages"]["part"]
+    losses = st["losses"]
+    opt_cfg = config.get("optimizer", {})
+    T = lambda t: t.detach().to(dev, torch.float32).contiguous()
+    mk, pose, root, ob = T(markers_subset), T(pose_body), T(root_orient), T(o_betas).reshape(1, -1)
+    F, Ms = mk.shape[:2]
+    NB = ob.shape[1]
+    twin = smpl.visiting_twin()
+    V = smpl.handle.V
+    vertex_labels = torch.argmax(smpl.lbs_weights, dim=-1)                                  # :438-439
+    results: List[Dict] = []
+    for g0 in range(0, len(subtrees), max_groups):
+        chunk = [list(int(j) for j in s) for s in subtrees[g0:g0 + max_groups]]
+        G = len(chunk)
+        keep_orig = torch.stack([torch.isin(vertex_labels, torch.tensor(s, device=dev)) for s in chunk])   # [G,V] :441-444
+        keep_rows = keep_orig[:, twin.visit_ids.long()].to(torch.uint8).contiguous()        # row numbering of the twin
+        rep = lambda t: t.repeat((G,) + (1,) * (t.dim() - 1)).contiguous()
+        mk_s, pose_s, root_s = rep(mk), rep(pose), rep(root)
+        prob = FitProblem(smpl, mk_s, pose_s, ob, None, groups=G)
+        pb = ParamBlock.build({"trans": rep(torch.median(mk, dim=1)[0]), "z_angle": torch.zeros(G),
+                               "betas": ob.repeat(G, 1)}, dev)
+        g_yaw = torch.zeros(G * F, dtype=torch.float32, device=dev)
+        g_pose = torch.zeros_like(pose_s)                                                    # pose is not a parameter here
+        gb_rows = torch.zeros((G * F, NB), dtype=torch.float32, device=dev)
+        w_ch, w_reg = float(losses["chamfer"]), float(losses.get("reg_betas", 0.0))
+        ob_g = ob.repeat(G, 1).contiguous()
+        L = _lib.lib()
+
+        def closure():
+            v, g = pb.views, pb.gviews
+            pb.grad.zero_()
+            prob.red.zero_()
+            yaw_rows = torch.repeat_interleave(v["z_angle"], F).contiguous()
+            brows = torch.repeat_interleave(v["betas"], F, dim=0).contiguous()
+            with torch.cuda.device(dev):
+                if prob.vertices is None:
+                    prob.vertices = torch.empty((G * F, V, 3), dtype=torch.float32, device=dev)
+                check(L.uuo_lbs_forward(twin.handle.handle, ptr(brows), G * F, ptr(root_s), ptr(pose_s), POSE_ROTMAT,
+                                        ptr(yaw_rows), ptr(v["trans"]), G * F, ptr(prob.vertices), None, ptr(prob.ws),
+                                        prob._st()))                                         # :458-466 (pose used as it is)
+                check(L.uuo_mask_vertices(ptr(prob.vertices), ptr(keep_rows), G * F, V, F, 1.0e18, prob._st()))
+                check(L.uuo_nn_argmin_presorted_fit(ptr(mk_s), ptr(prob.vertices), ptr(twin.visit_ids), None, ptr(prob.pos),
+                                                    G * F, Ms, V, ptr(prob.d2), ptr(prob.idx), ptr(prob.pos), prob._st()))
+                check(L.uuo_chamfer_rows(ptr(mk_s), ptr(prob.vertices), None, ptr(prob.pos), G * F, Ms, V,
+                                         w_ch / (F * Ms), ptr(prob.loss_slot), ptr(prob.g_rows), prob._st()))   # :471-476
+                fn = L.uuo_lbs_backward_rows
+                if Ms <= 64:             # v_posed of the matched rows straight out of the dense forward's workspace
+                    check(L.uuo_lbs_cache_vposed_rows(twin.handle.handle, G * F, ptr(prob.pos), Ms, ptr(prob.ws), prob._st()))
+                    fn = L.uuo_lbs_backward_rows_cached
+                check(fn(smpl.handle.handle, ptr(brows), G * F, ptr(root_s), ptr(pose_s), POSE_ROTMAT, ptr(yaw_rows), G * F,
+                         ptr(prob.idx), 0, Ms, ptr(prob.g_rows), None, ptr(prob.ws), ptr(gb_rows), None, ptr(g_pose),
+                         ptr(g_yaw), ptr(g["trans"]), prob._st()))
+            g["z_angle"].copy_(g_yaw.view(G, F).sum(1))                                      # one yaw per candidate
+            g["betas"].copy_(gb_rows.view(G, F, NB).sum(1))
+            if w_reg != 0.0:                                                                 # :516-517
+                prob.sqdiff(v["betas"], ob_g, w_reg / NB, g["betas"])
+            return prob.loss_slot[0]
+
+        iters = int(st["num_iters"])
+        if iters > 0:
+            run_adam(pb, closure, iters, float(st.get("lr_adam", opt_cfg.get("lr", 0.01))))
+        with torch.no_grad():
+            for gi, subtree in enumerate(chunk):
+                z = pb.views["z_angle"][gi].reshape(1, 1, 1).clone()
+                trans = pb.views["trans"][gi * F:(gi + 1) * F].clone()
+                betas = pb.views["betas"][gi:gi + 1].clone()
+                vidx = keep_orig[gi].nonzero(as_tuple=True)[0]
+                z_root = rot_z(z.expand(F, 1, 1)) @ root
+                out = smpl(betas=betas.expand(F, -1), body_pose=pose, global_orient=z_root, transl=trans, pose2rot=False)
+                vs = out.vertices[:, vidx].contiguous()
+                distance = float(chamfer_distance(mk, vs, single_directional=False)[0])     # :564-580
+                results.append({"subtree": subtree, "distance": distance, "loss": None, "betas": betas, "trans": trans,
+                                "root_orient": z_root.clone(), "z_angle": z, "vertex_indices": vidx,
+                                "vertices": out.vertices.detach()})
+    return results
+
+
 def find_best_part_fits(markers: torch.Tensor, pose_body: torch.Tensor, betas: torch.Tensor, root_orient: torch.Tensor,
                         marker_labels: torch.Tensor, smpl_inference, hierarchy, config: Dict,
                         subtrees: Optional[Sequence[Sequence[int]]] = None, iter_fn: Optional[Callable] = None) -> Dict:
@@ -161,7 +256,11 @@ def find_best_part_fits(markers: torch.Tensor, pose_body: torch.Tensor, betas: t
             subtrees = [list(range(parents.shape[0]))]                                      # :396-397
         else:
             subtrees = sub_hierarchies(parents, len(chain))                                 # :399
-    fits = fit_subtrees(markers_subset, pose_body, betas, root_orient, smpl, subtrees, config, iter_fn)
+    batched = str(config.get("optimizer", {}).get("name", "lbfgs")).lower() == "adam" and iter_fn is None
+    if batched:      # independent fits -> hypothesis groups of one stacked problem (fused Adam, graph replay)
+        fits = fit_subtrees_batched(markers_subset, pose_body, betas, root_orient, smpl, subtrees, config)
+    else:            # the reference's optimiser: one L-BFGS (own line search, own stopping test) per candidate
+        fits = fit_subtrees(markers_subset, pose_body, betas, root_orient, smpl, subtrees, config, iter_fn)
     ranked = sorted(fits, key=lambda r: r["distance"])
     best = ranked[0]
     final_labels = torch.zeros_like(marker_labels)
