@@ -621,8 +621,9 @@ def run_fit(args, rank, world, local, dev, light=False):
                 roofline.update(table[dom])
                 roofline["peak_source"] = peaks["src"] + (" (TF32 dense = bf16/2; logical flops, the split issues 2-3 MMAs per product)"
                                                           if table[dom]["bound"] == "tensor" else "")
-                # ncu captures of the fit kernels were taken at F = 5000 per launch
-                roofline["traffic"] = traffic.get(dom) if F == 5000 and dom in FIT_TRAFFIC_KEYS else None
+                # ncu captures (dram bytes per launch) exist for F = 5000 (flat keys) and F = 100000 (the default at N = 1)
+                by_size = traffic.get("F%d" % F, {})
+                roofline["traffic"] = by_size.get(dom, traffic.get(dom) if F == 5000 and dom in FIT_TRAFFIC_KEYS else None)
             roofline["per_kernel"] = table
         cpu = tg = None
         if world == 1 and not args.no_cpu_baseline:
