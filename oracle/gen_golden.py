@@ -5,7 +5,9 @@
 synthetic model through ``smplx.SMPL(data_struct=...)`` (body_models.py:57,132-143).
 ``closure_*.npz`` come from the oracle restatement (``oracle/closures.py``), because the
 reference's ``video_mocap`` package cannot be imported here (pytorch3d, igl, trimesh ...
-missing); they pin the oracle against drift, not against the reference.
+missing); they pin the oracle against drift.  The pin against the REFERENCE is ``closure_ref.npz``:
+``oracle/gen_golden_ref_closures.py`` compiles the reference's own stage functions from source and runs them on the
+inputs stored here.
 
     python -m oracle.gen_golden            # from the repo root
 """

@@ -1,6 +1,7 @@
 """GPU check of the tcgen05 3xTF32 GEMMs against the exact-fp32 SIMT kernels (UUO_GEMM_SIMT=1) through the
 SMPL layer: same inputs, compare vertices and every gradient; then per-kernel timings.
 
+    UUO_EXTRA_NVCC_FLAGS=-DUUO_DEBUG_SIMT python -m uuo_mocap_b200.build --force     # the release build has no SIMT path
     python tools/gemm_check.py [F ...]
 """
 import os
