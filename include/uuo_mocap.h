@@ -64,7 +64,9 @@ int uuo_model_info(const uuo_model* m, int what);
  * and its autograd backward.  The workspace written by forward is what backward reads. */
 size_t uuo_lbs_workspace_bytes(const uuo_model* m, int F);
 
-/* betas[betas_rows,NB], betas_rows in {1,F} (1 = one row shared by all frames, body_models.py:371-376);
+/* betas[betas_rows,NB], betas_rows = 1 (one row shared by all frames, body_models.py:371-376), F (one per frame), or a
+ * divisor G of F (G stacked hypothesis groups of F/G consecutive frames, each with its own row: the batched MHT loop of
+ * multimodal.py:462-606); gradients g_betas[betas_rows,NB] are summed over the frames of a row;
  * global_orient[F,1,...], body_pose[F,J-1,...] per pose_mode; yaw[F] or NULL: when given the root
  * matrix is Rz(yaw[f]) @ global_orient[f] (optimization.py:192,672-679) before pose_mode is applied;
  * transl[F,3] or NULL.  Outputs vertices[F,V,3], joints[F,J+NE,3]. */

@@ -174,3 +174,51 @@ def test_unaligned_caller_tensors(layers):
     for other in outs[1:]:
         for a, b in zip(outs[0], other):
             assert torch.equal(a, b)
+
+
+def test_betas_rows_per_group(layers):
+    """betas_rows = G (a divisor of F): G stacked hypothesis groups of F/G consecutive frames, one betas row each (the
+    batched MHT loop, multimodal.py:462-606) == the same rows expanded to one per frame; d betas summed per group."""
+    from uuo_mocap_b200 import synthetic
+    from uuo_mocap_b200.smpl import lbs_apply
+    smpl, _ = layers["top4"]
+    F, G = 12, 3
+    mb = synthetic.make_lbs_microbench(F, seed=17)
+    rot = torch.from_numpy(mb["rot"]).cuda()
+    tr = torch.from_numpy(mb["transl"]).cuda()
+    gv, gj = torch.from_numpy(mb["g_vertices"]).cuda(), torch.from_numpy(mb["g_joints"]).cuda()
+    bG = torch.from_numpy(mb["betas"][:G]).cuda().requires_grad_(True)
+    bF = bG.detach().repeat_interleave(F // G, dim=0).requires_grad_(True)
+    outs = []
+    for b in (bG, bF):
+        v, j = lbs_apply(smpl.handle, b, rot[:, :1].contiguous(), rot[:, 1:].contiguous(), tr)
+        torch.autograd.backward([v, j], [gv, gj])
+        outs.append((v.detach(), j.detach(), b.grad))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    want = outs[1][2].view(G, F // G, -1).sum(1)
+    assert rel_err(outs[0][2].cpu().numpy(), want.cpu().numpy()) < 1e-6
+    with pytest.raises(ValueError):
+        lbs_apply(smpl.handle, torch.zeros(5, 10, device="cuda"), rot[:, :1].contiguous(), rot[:, 1:].contiguous(), tr)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two CUDA devices in one process")
+def test_two_devices_in_one_process(get_model):
+    """Launch configuration (SM count, > 48 KB dynamic-smem opt-in) is cached per DEVICE (csrc/devcfg.cu): a model on
+    cuda:1 created after cuda:0 was used in the same process gives the same results."""
+    from uuo_mocap_b200 import ops, synthetic
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    m = get_model("top4")
+    mb = synthetic.make_lbs_microbench(6, seed=4)
+    cap = synthetic.make_capture(m, 6, num_markers=41, seed=9)
+    outs = []
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        smpl = SMPL(_as_struct(m), device=dev)
+        rot = torch.from_numpy(mb["rot"]).to(dev).requires_grad_(True)
+        o = smpl(betas=torch.from_numpy(mb["betas"]).to(dev), body_pose=rot[:, 1:], global_orient=rot[:, :1],
+                 transl=torch.from_numpy(mb["transl"]).to(dev), pose2rot=False)
+        (o.vertices * torch.from_numpy(mb["g_vertices"]).to(dev)).sum().backward()
+        d, i = ops.nn_argmin(torch.from_numpy(cap.markers).to(dev), o.vertices.detach().contiguous(), smpl.handle)
+        outs.append((o.vertices.detach().cpu(), rot.grad.cpu(), d.cpu(), i.cpu()))
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            assert torch.equal(a, b)

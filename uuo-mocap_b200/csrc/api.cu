@@ -6,7 +6,7 @@ static int check_common(const uuo_model* m, const float* betas, int betas_rows, 
   UUO_CHECK_ARG(m != nullptr, "model is NULL");
   UUO_CHECK_ARG(F > 0, "F must be positive");
   UUO_CHECK_ARG(betas && go && bp, "betas / global_orient / body_pose is NULL");
-  UUO_CHECK_ARG(betas_rows == 1 || betas_rows == F, "betas_rows must be 1 or F");
+  UUO_CHECK_ARG(betas_rows >= 1 && betas_rows <= F && F % betas_rows == 0, "betas_rows must be 1, F or a divisor of F");
   UUO_CHECK_ARG(pose_mode >= 0 && pose_mode <= 2, "bad pose_mode");
   UUO_CHECK_ARG(workspace != nullptr, "workspace is NULL");
   UUO_CHECK_ARG(((uintptr_t)workspace & 15) == 0, "workspace must be 16-byte aligned");

@@ -215,7 +215,8 @@ __global__ void __launch_bounds__(128) fk_forward_kernel(
   if (f >= F) return;
   const int J = tree.J;
   const int ne = (pose_mode == UUO_POSE_AXISANGLE) ? 3 : 9;
-  const float* betas_f = betas + (betas_rows == 1 ? 0 : (size_t)f * NB);
+  // betas_rows in {1, G, F} with G | F: row of frame f (G stacked hypothesis groups of F / G consecutive frames each)
+  const float* betas_f = betas + (size_t)(betas_rows == 1 ? 0 : f / (F / betas_rows)) * NB;
   LaneFK s;
   fk_lane_forward(tree, J0, Jdirs, NB, betas_f, go + (size_t)f * ne, bp + (size_t)f * (J - 1) * ne, pose_mode,
                   yaw ? yaw + f : nullptr, lane, s);
@@ -260,7 +261,8 @@ __global__ void __launch_bounds__(128) fk_backward_kernel(
   const bool act = lane < J;
   const int jl = act ? lane : 0;
   const int ne = (pose_mode == UUO_POSE_AXISANGLE) ? 3 : 9;
-  const float* betas_f = betas + (betas_rows == 1 ? 0 : (size_t)f * NB);
+  // betas_rows in {1, G, F} with G | F: row of frame f (G stacked hypothesis groups of F / G consecutive frames each)
+  const float* betas_f = betas + (size_t)(betas_rows == 1 ? 0 : f / (F / betas_rows)) * NB;
   LaneFK s;
   fk_lane_forward(tree, J0, Jdirs, NB, betas_f, go + (size_t)f * ne, bp + (size_t)f * (J - 1) * ne, pose_mode,
                   yaw ? yaw + f : nullptr, lane, s);
@@ -449,8 +451,11 @@ __global__ void __launch_bounds__(128) fk_backward_kernel(
 // ONE CTA of 1024 threads: thread t sums frames t, t + 1024, ... for all 16 slots of a frame (one 64 B row per load,
 // rows of consecutive threads are consecutive), then a fixed-order tree over the threads.  (The r1g version ran one
 // 256-thread CTA per beta with 4 B loads 64 B apart: 14 us at F = 5000, 3 % of a fitting iteration.)
+// one CTA per betas row: g_betas[g] = sum over the row's F frames (frames g F .. g F + F - 1)
 __global__ void __launch_bounds__(1024) reduce_gbetas_kernel(const float* __restrict__ gbetas_f, int F, int NB,
                                                              float* __restrict__ g_betas) {
+  gbetas_f += (size_t)blockIdx.x * F * 16;
+  g_betas += (size_t)blockIdx.x * NB;
   __shared__ float sh[32][17];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   float a[16];
@@ -509,7 +514,7 @@ int launch_fk_backward(const uuo_model* m, const float* betas, int betas_rows, c
                                              g_yaw, g_transl);
   } UUO_LAUNCH_CHECK();
   if (g_betas) {
-    if (betas_rows == 1) reduce_gbetas_kernel<<<1, 1024, 0, st>>>(ws.gbetas, F, m->NB, g_betas);
+    if (betas_rows < F) reduce_gbetas_kernel<<<betas_rows, 1024, 0, st>>>(ws.gbetas, F / betas_rows, m->NB, g_betas);
     else copy_gbetas_kernel<<<(F * m->NB + 255) / 256, 256, 0, st>>>(ws.gbetas, F, m->NB, g_betas);
     UUO_LAUNCH_CHECK();
   }

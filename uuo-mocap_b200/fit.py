@@ -128,17 +128,16 @@ class FitProblem:
                                                self._st()))
 
     def betas_rows(self, betas):
-        """[G,NB] parameter -> rows handed to the kernels ([1,NB] shared, or [F,NB] for stacked hypotheses)."""
-        if self.groups == 1:
-            return betas.reshape(1, -1)
-        return torch.repeat_interleave(betas.reshape(self.groups, -1), self.F // self.groups, dim=0).contiguous()
+        """[G,NB] parameter -> rows handed to the kernels: one row per hypothesis group (betas_rows = G; G = 1: the row
+        shared by all frames).  The kernels map frame f to row f // (F / G)."""
+        return betas.reshape(self.groups, -1)
 
     def reduce_gbetas(self, g_betas_param):
-        """d/d betas and the loss: (a) stacked hypotheses: per-frame rows -> one row per group; (b) ONE sum over the
-        shards of the [G,16] block (peer-memory kernel when the shard has a PeerComm, else torch.distributed)."""
+        """d/d betas and the loss: the kernels leave one d/d betas row per hypothesis group; ONE sum over the shards of the
+        [G,16] block (peer-memory kernel when the shard has a PeerComm, else torch.distributed)."""
         nb = self.mh.NB
         if self.groups > 1:
-            self.red[:, :nb] = self.gbetas_rows.view(self.groups, self.F // self.groups, -1).sum(1)
+            self.red[:, :nb] = self.gbetas_rows
         self.shard.iter_all_reduce_sum_(self.red)
         g_betas_param.copy_(self.red[:, :nb].reshape(g_betas_param.shape))
 
@@ -146,7 +145,7 @@ class FitProblem:
         if self.groups == 1:
             return self.red
         if self.gbetas_rows is None:
-            self.gbetas_rows = torch.empty((self.F, self.mh.NB), dtype=torch.float32, device=self.dev)
+            self.gbetas_rows = torch.empty((self.groups, self.mh.NB), dtype=torch.float32, device=self.dev)
         return self.gbetas_rows
 
 

@@ -177,7 +177,7 @@ def fit_subtrees_batched(markers_subset: torch.Tensor, pose_body: torch.Tensor, 
                                "betas": ob.repeat(G, 1)}, dev)
         g_yaw = torch.zeros(G * F, dtype=torch.float32, device=dev)
         g_pose = torch.zeros_like(pose_s)                                                    # pose is not a parameter here
-        gb_rows = torch.zeros((G * F, NB), dtype=torch.float32, device=dev)
+        gb_rows = torch.zeros((G, NB), dtype=torch.float32, device=dev)                     # one d/d betas row per candidate
         w_ch, w_reg = float(losses["chamfer"]), float(losses.get("reg_betas", 0.0))
         ob_g = ob.repeat(G, 1).contiguous()
         L = _lib.lib()
@@ -187,11 +187,11 @@ def fit_subtrees_batched(markers_subset: torch.Tensor, pose_body: torch.Tensor, 
             pb.grad.zero_()
             prob.red.zero_()
             yaw_rows = torch.repeat_interleave(v["z_angle"], F).contiguous()
-            brows = torch.repeat_interleave(v["betas"], F, dim=0).contiguous()
+            brows = v["betas"]                                                               # betas_rows = G: row f // F
             with torch.cuda.device(dev):
                 if prob.vertices is None:
                     prob.vertices = torch.empty((G * F, V, 3), dtype=torch.float32, device=dev)
-                check(L.uuo_lbs_forward(twin.handle.handle, ptr(brows), G * F, ptr(root_s), ptr(pose_s), POSE_ROTMAT,
+                check(L.uuo_lbs_forward(twin.handle.handle, ptr(brows), G, ptr(root_s), ptr(pose_s), POSE_ROTMAT,
                                         ptr(yaw_rows), ptr(v["trans"]), G * F, ptr(prob.vertices), None, ptr(prob.ws),
                                         prob._st()))                                         # :458-466 (pose used as it is)
                 check(L.uuo_mask_vertices(ptr(prob.vertices), ptr(keep_rows), G * F, V, F, 1.0e18, prob._st()))
@@ -203,11 +203,11 @@ def fit_subtrees_batched(markers_subset: torch.Tensor, pose_body: torch.Tensor, 
                 if Ms <= 64:             # v_posed of the matched rows straight out of the dense forward's workspace
                     check(L.uuo_lbs_cache_vposed_rows(twin.handle.handle, G * F, ptr(prob.pos), Ms, ptr(prob.ws), prob._st()))
                     fn = L.uuo_lbs_backward_rows_cached
-                check(fn(smpl.handle.handle, ptr(brows), G * F, ptr(root_s), ptr(pose_s), POSE_ROTMAT, ptr(yaw_rows), G * F,
+                check(fn(smpl.handle.handle, ptr(brows), G, ptr(root_s), ptr(pose_s), POSE_ROTMAT, ptr(yaw_rows), G * F,
                          ptr(prob.idx), 0, Ms, ptr(prob.g_rows), None, ptr(prob.ws), ptr(gb_rows), None, ptr(g_pose),
                          ptr(g_yaw), ptr(g["trans"]), prob._st()))
             g["z_angle"].copy_(g_yaw.view(G, F).sum(1))                                      # one yaw per candidate
-            g["betas"].copy_(gb_rows.view(G, F, NB).sum(1))
+            g["betas"].copy_(gb_rows)
             if w_reg != 0.0:                                                                 # :516-517
                 prob.sqdiff(v["betas"], ob_g, w_reg / NB, g["betas"])
             return prob.loss_slot[0]

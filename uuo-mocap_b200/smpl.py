@@ -133,7 +133,8 @@ class _LBSFunction(torch.autograd.Function):
 
 
 def lbs_apply(mh: ModelHandle, betas, global_orient, body_pose, transl=None, yaw=None, pose_mode=POSE_ROTMAT):
-    """Functional form used by SMPL.forward and the tests.  Shapes: betas [1|F,NB];
+    """Functional form used by SMPL.forward and the tests.  Shapes: betas [1|G|F,NB] (G | F: one row per group of F/G
+    consecutive frames, the stacked hypotheses of the batched MHT loop);
     rot modes: global_orient [F,1,3,3], body_pose [F,J-1,3,3]; axis-angle: [F,1,3] / [F,J-1,3]."""
     F = global_orient.shape[0]
     J = mh.J
@@ -141,8 +142,8 @@ def lbs_apply(mh: ModelHandle, betas, global_orient, body_pose, transl=None, yaw
         go, bp = global_orient.reshape(F, 1, 3), body_pose.reshape(F, J - 1, 3)
     else:
         go, bp = global_orient.reshape(F, 1, 3, 3), body_pose.reshape(F, J - 1, 3, 3)
-    if betas.shape[0] not in (1, F):
-        raise ValueError("betas batch (%d) must be 1 or the pose batch (%d)" % (betas.shape[0], F))
+    if betas.shape[0] < 1 or betas.shape[0] > F or F % betas.shape[0]:
+        raise ValueError("betas batch (%d) must be 1, the pose batch (%d) or a divisor of it" % (betas.shape[0], F))
     if betas.shape[1] != mh.NB:
         raise ValueError("betas must have %d columns" % mh.NB)
     if yaw is not None:
