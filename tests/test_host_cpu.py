@@ -249,3 +249,31 @@ def test_lbfgs_is_refused_across_shards():
         _optimise(None, lambda: None, {"num_iters": 5}, {"name": "lbfgs"}, 0.1, None, Shard(0, 2))
     with pytest.raises(NotImplementedError):       # no name = the reference's optimiser = L-BFGS
         _optimise(None, lambda: None, {"num_iters": 5}, {}, 0.1, None, Shard(1, 2))
+
+
+def test_bench_reference_arm_line(tmp_path):
+    """`bench.py --impl reference` (the driver's CPU arm) prints ONE JSON line with the contract's keys, on the same
+    `config` object as the GPU arm (bench.fit_config), from a bounded frame sample.  Tiny sample here: seconds."""
+    import json
+    import subprocess
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                          "--ref-frames", "12"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "frame_iters_per_sec" and d["unit"] == "frame-iters/s"
+    assert d["higher_is_better"] is True and d["steps"] == 2 and d["value"] > 0 and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and "12-frame" in d["cpu_baseline"]["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    sys.path.insert(0, ROOT)
+    import argparse
+    import importlib
+    saved = (os.dup(1),)
+    try:
+        bench = importlib.import_module("bench")       # (bench redirects fd 1 to stderr at import: restore it afterwards)
+    finally:
+        os.dup2(saved[0], 1)
+        os.close(saved[0])
+    want = bench.fit_config(argparse.Namespace(workload="fit100k", frames=0), 1)
+    assert d["config"] == want and "configs[4]" in d["config"]["workload"]
