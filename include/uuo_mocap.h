@@ -174,6 +174,18 @@ int uuo_marker_loss_rows(const float* markers, const float* virt, const float* m
 int uuo_mean_dist_accumulate(const float* markers, const float* vertices, const float* frame_mask, int F,
                              int M, int V, float* acc, void* stream);
 int uuo_mean_argmin(const float* acc, int M, int V, float count, int32_t* idx, void* stream);
+/* The same accumulation for callers that only want the per-marker argmin (the reference keeps nothing else of the
+ * [M,V] matrix: optimization.py:596-603).  bound[M] must be >= the smallest COMPLETE sum of each marker (over all the
+ * frames that will be added to acc, on every shard).  A sum that has passed bound[m] cannot be the minimum any more
+ * (the terms are >= 0 and fp32 addition is monotone), so the kernel stops evaluating it: on return an entry is either
+ * bit-equal to what uuo_mean_dist_accumulate leaves there, or a partial sum > bound[m].  The argmin is unchanged.
+ * uuo_mean_dist_candidate_sums gives the material for the bound: sums[m] (fp64, device) = the sum of the distances
+ * marker m <-> vertex cand[m] over the frames with frame_mask == 1; shards add their sums, and
+ * bound = sum * (1 + frames * 2^-23) covers the rounding of the in-order fp32 accumulation. */
+int uuo_mean_dist_accumulate_bounded(const float* markers, const float* vertices, const float* frame_mask, int F,
+                                     int M, int V, const float* bound, float* acc, void* stream);
+int uuo_mean_dist_candidate_sums(const float* markers, const float* vertices, const float* frame_mask, int F, int M,
+                                 int V, const int32_t* cand, double* sums, void* stream);
 
 /* ---- prior / regulariser terms of the closures (optimization.py:243-256,363-374) ----
  * g[i] += scale * 2 * (x[i]-y[i]) ; loss_sum[0] += scale * sum (x-y)^2 (caller folds 1/numel in scale) */

@@ -91,6 +91,43 @@ def test_compute_nearest_points(ctx, golden):
         assert abs(mean_ref[m, idx[m]] - mean_ref[m, r["np_vertex_idx"][m]]) <= 1e-6 * mean_ref[m, idx_ref[m]]
 
 
+@pytest.mark.parametrize("permute", [False, True])
+def test_compute_nearest_points_bounded_path(get_model, permute, monkeypatch):
+    """compute_nearest_points(use_mean) picks the bounded mean-distance kernel when a marker column follows one point of
+    the body (trajectories) and the plain kernel for shuffled columns; forcing either path gives the same indices."""
+    from uuo_mocap_b200 import fit, ops, synthetic
+    from uuo_mocap_b200.smpl import SMPL, _as_struct
+    model = get_model("top4")
+    smpl = SMPL(_as_struct(model), device="cuda:0")
+    F = 220
+    cap = synthetic.make_capture(model, F, num_markers=41, seed=9, n_ghost=4, dropout_p=0.05, noise_std=0.002,
+                                 permute=permute)
+    mk = torch.from_numpy(cap.markers).cuda()
+    rot = synthetic.axis_angle_to_matrix_np(cap.gt_pose_aa.astype(np.float64)).astype(np.float32)
+    args = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (rot[:, 1:], cap.gt_betas, rot[:, :1], cap.gt_trans)]
+    img_mask = torch.ones(F)
+    img_mask[[0, 7]] = 0
+    used = []
+    real = ops.mean_distance_accumulate_bounded
+    monkeypatch.setattr(ops, "mean_distance_accumulate_bounded", lambda *a, **k: (used.append(1), real(*a, **k))[1])
+    run = lambda: fit.compute_nearest_points(mk, args[0], args[1], args[2], args[3], smpl, img_mask=img_mask,
+                                             as_one_hot=False)
+    idx_auto = run()
+    assert bool(used) == (not permute)
+    monkeypatch.setattr(fit, "BOUNDED_MIN_RATIO", 0.0)
+    idx_bounded = run()
+    monkeypatch.setattr(fit, "BOUNDED_MIN_RATIO", float("inf"))
+    idx_plain = run()
+    assert torch.equal(idx_auto, idx_plain) and torch.equal(idx_bounded, idx_plain)
+    if not permute:      # the columns are trajectories: the pick is the attachment vertex or a neighbour of it
+        own = torch.from_numpy(cap.marker_vertex_ids).cuda()
+        with torch.no_grad():
+            v0 = smpl(betas=args[1], body_pose=args[0][:1], global_orient=args[2][:1], transl=args[3][:1],
+                      pose2rot=False).vertices[0]
+        d = (v0[idx_plain[:41].long()] - v0[own]).norm(dim=-1)
+        assert float(d.median()) < 0.05
+
+
 def test_optim_chamfer_bakes_yaw_like_the_reference(ctx, golden):
     """optim_chamfer with zero iterations of change: root_orient[:] = Rz(z) @ root_orient (optimization.py:280-285),
     against the tensor the reference's own function left behind."""

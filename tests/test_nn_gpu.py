@@ -89,6 +89,91 @@ def test_mean_distance_argmin(get_model, F, M, V):
         assert np.array_equal(a2.cpu().numpy(), acc)
 
 
+def _bounded_case(F, M, V, seed, coherent):
+    """Markers that ride on the vertex cloud (a few cm off their vertex) so that a candidate vertex gives a tight
+    bound; ``coherent``: the vertex axis is sorted along x (tiles of neighbouring vertices, like the visiting order)."""
+    rng = np.random.default_rng(seed)
+    base = rng.normal(0, 0.5, size=(V, 3)).astype(np.float32)
+    if coherent:
+        base = base[np.argsort(base[:, 0])]
+    drift = np.cumsum(rng.normal(0, 0.01, size=(F, 1, 3)), axis=0).astype(np.float32)
+    v = (base[None] + drift + rng.normal(0, 0.002, size=(F, V, 3))).astype(np.float32)
+    on = rng.integers(0, V, size=M)
+    m = (v[:, on] + rng.normal(0, 0.01, size=(F, M, 3))).astype(np.float32)
+    if M > 3:
+        m[:, M - 1] += 3.0                        # a ghost marker far from everything
+    fm = np.ones(F, dtype=np.float32)
+    if F > 6:
+        fm[[0, 5]] = 0
+    return m, v, fm
+
+
+@pytest.mark.parametrize("F,M,V,coherent", [(150, 45, 6890, True), (150, 45, 6890, False), (37, 2, 100, True),
+                                            (64, 70, 500, True), (3, 1, 1, True), (33, 46, 49, False)])
+def test_mean_distance_bounded(F, M, V, coherent):
+    """uuo_mean_dist_accumulate_bounded: every entry at or below the bound is BIT-equal to the unbounded kernel, every
+    other entry is above the bound, the per-marker argmin is the same; the candidate sums equal numpy's in fp64."""
+    from uuo_mocap_b200 import ops
+    m, v, fm = _bounded_case(F, M, V, 11 + F + M, coherent)
+    mt, vt, fmt = torch.from_numpy(m).cuda(), torch.from_numpy(v).cuda(), torch.from_numpy(fm).cuda()
+    sel = np.where(fm == 1)[0]
+    idx_full, acc_full = ops.mean_distance_argmin(mt, vt, fmt)
+    f0 = int(sel[0])
+    cand, _ = ops.mean_distance_argmin(mt[f0:f0 + 1].contiguous(), vt[f0:f0 + 1].contiguous())
+    sums = ops.mean_distance_candidate_sums(mt, vt, cand, fmt)
+    c = cand.cpu().numpy().astype(np.int64)
+    ref = np.zeros(M, dtype=np.float64)
+    for f in sel:
+        ref += np.linalg.norm(v[f, c] - m[f], axis=-1).astype(np.float64)      # fp32 distances, fp64 sum
+    np.testing.assert_allclose(sums.cpu().numpy(), ref, rtol=1e-12, atol=0)
+    bound = ops.mean_bound_from_sums(sums, len(sel))
+    full = acc_full.cpu().numpy()
+    b = bound.cpu().numpy()
+    assert (full[np.arange(M), c] <= b).all()          # the candidate's own in-order fp32 sum is under the bound
+    acc_b = ops.mean_distance_accumulate_bounded(mt, vt, bound, fmt).cpu().numpy()
+    keep = full <= b[:, None]
+    assert np.array_equal(acc_b[keep], full[keep])
+    assert (acc_b[~keep] > np.broadcast_to(b[:, None], full.shape)[~keep]).all()
+    assert (acc_b <= full).all()
+    idx_b = ops.mean_argmin(torch.from_numpy(acc_b).cuda(), float(len(sel)))
+    assert torch.equal(idx_b, idx_full)
+    if V >= 500 and F >= 64:
+        assert (acc_b < full).mean() > 0.5             # most far pairs were cut early
+    # frame ranges (the shards): every range is cut against the GLOBAL bound, the per-range results are added up
+    if F >= 9:
+        tot = np.zeros_like(full)
+        for lo, hi in ((0, F // 3), (F // 3, F // 2), (F // 2, F)):
+            a = ops.mean_distance_accumulate_bounded(mt[lo:hi].contiguous(), vt[lo:hi].contiguous(), bound,
+                                                     fmt[lo:hi].contiguous())
+            tot = tot + a.cpu().numpy()
+        idx_r = ops.mean_argmin(torch.from_numpy(tot).cuda(), float(len(sel)))
+        parts = np.zeros_like(full)
+        for lo, hi in ((0, F // 3), (F // 3, F // 2), (F // 2, F)):
+            _, a = ops.mean_distance_argmin(mt[lo:hi].contiguous(), vt[lo:hi].contiguous(), fmt[lo:hi].contiguous(),
+                                            finalize=False)
+            parts = parts + a.cpu().numpy()
+        idx_p = ops.mean_argmin(torch.from_numpy(parts).cuda(), float(len(sel)))
+        assert torch.equal(idx_r, idx_p)
+
+
+def test_mean_distance_bounded_keeps_accumulating():
+    """Two calls on consecutive frame ranges with the same ``acc`` == one call (entries under the bound)."""
+    from uuo_mocap_b200 import ops
+    F, M, V = 90, 45, 1000
+    m, v, fm = _bounded_case(F, M, V, 5, True)
+    mt, vt, fmt = torch.from_numpy(m).cuda(), torch.from_numpy(v).cuda(), torch.from_numpy(fm).cuda()
+    _, full = ops.mean_distance_argmin(mt, vt, fmt, finalize=False)
+    cand, _ = ops.mean_distance_argmin(mt[1:2].contiguous(), vt[1:2].contiguous())
+    bound = ops.mean_bound_from_sums(ops.mean_distance_candidate_sums(mt, vt, cand, fmt), F)
+    h = 40
+    acc = ops.mean_distance_accumulate_bounded(mt[:h].contiguous(), vt[:h].contiguous(), bound, fmt[:h].contiguous())
+    acc = ops.mean_distance_accumulate_bounded(mt[h:].contiguous(), vt[h:].contiguous(), bound, fmt[h:].contiguous(),
+                                               acc=acc)
+    keep = full <= bound[:, None]
+    assert torch.equal(acc[keep], full[keep])
+    assert bool((acc[~keep] > bound[:, None].expand_as(acc)[~keep]).all())
+
+
 # ---- pruned (box-bounded) kernel: same outputs bit for bit, for ANY permutation ----
 @pytest.mark.parametrize("F,M,V", [(1, 1, 1), (3, 41, 6890), (5, 45, 6890), (2, 7, 19), (3, 300, 515), (4, 256, 1000),
                                    (2, 9, 8192), (2, 5, 8200)])

@@ -41,6 +41,8 @@ SIGNATURES = {
     "uuo_marker_loss_rows": (_I, [_P, _P, _P, _I, _F, _F, _P, _P, _P]),
     "uuo_mean_dist_accumulate": (_I, [_P, _P, _P, _I, _I, _I, _P, _P]),
     "uuo_mean_argmin": (_I, [_P, _I, _I, _F, _P, _P]),
+    "uuo_mean_dist_accumulate_bounded": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
+    "uuo_mean_dist_candidate_sums": (_I, [_P, _P, _P, _I, _I, _I, _P, _P, _P]),
     "uuo_sqdiff_accumulate": (_I, [_P, _P, _SZ, _F, _P, _P, _P]),
     "uuo_temporal_accumulate": (_I, [_P, _P, _P, _I, _I, _F, _P, _P, _P]),
     "uuo_mask_vertices": (_I, [_P, _P, _I, _I, _I, _F, _P]),

@@ -58,8 +58,10 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     if failed:
         raise RuntimeError("nvcc failed")
     if force or procs or _stale(LIB, objs):
-        cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+        tmp = LIB + ".tmp%d" % os.getpid()         # link beside the target, then rename: readers never see half a file
+        cmd = [nvcc, "-shared", "-o", tmp] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
         subprocess.check_call(cmd)
+        os.replace(tmp, LIB)
     return LIB
 
 

@@ -495,6 +495,10 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
             raise NotImplementedError("compute_locations.use_barycentric needs igl / trimesh (not on the CUDA path)")
         use_mean = bool(cl.get("use_mean", True))
     smpl = _model_of(smpl_inference)
+    if use_mean:
+        # the mean-distance kernel cuts (marker, vertex tile) pairs that can no longer win: that needs tiles of
+        # neighbouring vertices, i.e. the visiting-order twin (same body, vertices renumbered; fit.FitProblem uses it too)
+        smpl = smpl.visiting_twin()
     mh = smpl.handle
     dev = mh.device
     shard = shard or Shard()
@@ -513,11 +517,11 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
     if fm is not None and fm.numel() != F:
         raise ValueError("img_mask must hold one entry per frame (%d), got %d" % (F, fm.numel()))
     if use_mean:
-        _, acc = ops.mean_distance_argmin(mk, vertices, fm, finalize=False)
-        cnt = torch.tensor([float(F if fm is None else (fm == 1).sum().item())], dtype=torch.float64)
-        cnt = shard.all_reduce_sum(cnt)
-        shard.all_reduce_sum_(acc)                                                   # [M,V] fp32, once per stage
-        idx = ops.mean_argmin(acc, max(float(cnt.item()), 1.0))
+        acc, cnt = _mean_distance_sums(mk, vertices, fm, shard)
+        ids = smpl.visit_ids.long()
+        acc_model = torch.empty_like(acc)                                            # back to the model's numbering:
+        acc_model[:, ids] = acc                                                      # the FIRST minimum wins there
+        idx = ops.mean_argmin(acc_model, max(cnt, 1.0))
     else:
         idx = _closest_point_last_frames(mk, vertices, fm, marker_labels, granularity, pose.shape[1], shard)
     if not as_one_hot:
@@ -525,6 +529,51 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
     one_hot = torch.zeros((M, mh.V), dtype=torch.float32, device=dev)                # :601-603
     one_hot[torch.arange(M, device=dev), idx.long()] = 1.0
     return one_hot
+
+
+BOUNDED_MIN_RATIO = 2.0      # probe sum / candidate sum from which the bounded mean-distance kernel is used
+
+
+def _mean_distance_sums(mk, vertices, fm, shard):
+    """[M,V] sums of the marker-vertex distances over the valid frames of ALL shards (optimization.py:479-486,596-599),
+    exact wherever the per-marker minimum can be; returns (acc, number of valid frames).  One vertex per marker -- the
+    nearest one in the first valid frame of the lowest rank that has one -- gives an upper bound of the minimum
+    (uuo_mean_dist_candidate_sums, summed over the shards), which lets uuo_mean_dist_accumulate_bounded stop early on
+    everything that is far away."""
+    F, M = mk.shape[:2]
+    dev = mk.device
+    valid = torch.ones(F, dtype=torch.bool, device=dev) if fm is None else fm == 1
+    n_valid = int(valid.sum().item())
+    counts = torch.zeros(max(shard.world, 1), dtype=torch.float64)
+    counts[shard.rank] = n_valid
+    counts = shard.all_reduce_sum(counts)
+    total = int(counts.sum().item())
+    acc = torch.zeros((M, vertices.shape[1]), dtype=torch.float32, device=dev)
+    if total == 0:
+        return acc, 0.0
+    owner = int((counts > 0).nonzero()[0].item())
+    cand = torch.zeros(M, dtype=torch.float32, device=dev)
+    if shard.rank == owner:
+        f0 = int(valid.nonzero()[0].item())
+        vi, _ = ops.mean_distance_argmin(mk[f0:f0 + 1].contiguous(), vertices[f0:f0 + 1].contiguous())
+        cand = vi.to(torch.float32)
+    shard.all_reduce_sum_(cand)                                                      # vertex ids < 2^24: exact
+    cand = cand.to(torch.int32)
+    # the candidates' sums, and as a probe the sums of vertices elsewhere on the body (the candidate of another marker)
+    both = torch.cat([ops.mean_distance_candidate_sums(mk, vertices, cand, fm),
+                      ops.mean_distance_candidate_sums(mk, vertices, torch.roll(cand, M // 2), fm)])
+    shard.all_reduce_sum_(both)
+    sums, probe = both[:M], both[M:]
+    # The bound only cuts work when a marker column follows ONE point of the body, so that far vertices collect much
+    # larger sums than the candidate.  Columns that hold a different marker in every frame (shuffled clouds) give all
+    # vertices about the same sum: then nothing can be cut and the plain kernel (wider tiles, no checks) is faster.
+    if M > 1 and float(torch.median(probe / sums.clamp_min(1e-30)).item()) >= BOUNDED_MIN_RATIO:
+        bound = ops.mean_bound_from_sums(sums, total)
+        ops.mean_distance_accumulate_bounded(mk, vertices, bound, fm, acc)
+    else:
+        ops.mean_distance_argmin(mk, vertices, fm, acc=acc, finalize=False)
+    shard.all_reduce_sum_(acc)                                                       # [M,V] fp32, once per stage
+    return acc, float(total)
 
 
 def _closest_point_last_frames(mk, vertices, fm, marker_labels, granularity, num_joints, shard):

@@ -123,6 +123,62 @@ def mean_distance_argmin(markers: torch.Tensor, vertices: torch.Tensor, frame_ma
     return mean_argmin(acc, max(count, 1.0)), acc
 
 
+def mean_distance_candidate_sums(markers: torch.Tensor, vertices: torch.Tensor, cand: torch.Tensor,
+                                 frame_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """sums[m] (float64) = sum over the frames with frame_mask == 1 of ||vertices[f, cand[m]] - markers[f, m]||: the
+    material for the bound of ``mean_distance_accumulate_bounded`` (uuo_mean_dist_candidate_sums)."""
+    markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
+    F, M, _ = markers.shape
+    V = vertices.shape[1]
+    if vertices.shape[0] != F:
+        raise ValueError("markers and vertices must have the same number of frames")
+    cand = cand.to(markers.device, torch.int32).contiguous()
+    if cand.numel() != M:
+        raise ValueError("one candidate vertex per marker (%d), got %d" % (M, cand.numel()))
+    fm = _req(frame_mask, "frame_mask") if frame_mask is not None else None
+    if fm is not None and fm.numel() != F:
+        raise ValueError("frame_mask must hold one entry per frame (%d), got %d" % (F, fm.numel()))
+    sums = torch.zeros((M,), dtype=torch.float64, device=markers.device)
+    with torch.cuda.device(markers.device):
+        check(_lib.lib().uuo_mean_dist_candidate_sums(ptr(markers), ptr(vertices), ptr(fm), F, M, V, ptr(cand),
+                                                      ptr(sums), stream_ptr(markers.device)))
+    return sums
+
+
+def mean_bound_from_sums(sums: torch.Tensor, frames: int) -> torch.Tensor:
+    """fp32 bound >= the in-order fp32 sum of the same terms: recursive summation of n non-negative terms is off by at
+    most (n-1) u / (1 - (n-1) u) relative (u = 2^-24), the shards' partial sums add ``world`` more roundings; twice
+    that plus 2^-10 is generous, and the result is rounded UP to fp32."""
+    rel = 2.0 ** -10 + max(int(frames), 1) * 2.0 ** -23
+    b = (sums.double() * (1.0 + rel)).to(torch.float32)
+    return torch.nextafter(b, torch.full_like(b, float("inf")))
+
+
+def mean_distance_accumulate_bounded(markers: torch.Tensor, vertices: torch.Tensor, bound: torch.Tensor,
+                                     frame_mask: Optional[torch.Tensor] = None,
+                                     acc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``mean_distance_argmin(finalize=False)`` for callers that only need the per-marker argmin: entries whose running
+    sum passes ``bound[m]`` stop being evaluated (uuo_mean_dist_accumulate_bounded; see include/uuo_mocap.h)."""
+    markers, vertices = _req(markers, "markers"), _req(vertices, "vertices")
+    F, M, _ = markers.shape
+    V = vertices.shape[1]
+    dev = markers.device
+    if vertices.shape[0] != F:
+        raise ValueError("markers and vertices must have the same number of frames")
+    bound = _req(bound, "bound")
+    if bound.numel() != M:
+        raise ValueError("one bound per marker (%d), got %d" % (M, bound.numel()))
+    if acc is None:
+        acc = torch.zeros((M, V), dtype=torch.float32, device=dev)
+    fm = _req(frame_mask, "frame_mask") if frame_mask is not None else None
+    if fm is not None and fm.numel() != F:
+        raise ValueError("frame_mask must hold one entry per frame (%d), got %d" % (F, fm.numel()))
+    with torch.cuda.device(dev):
+        check(_lib.lib().uuo_mean_dist_accumulate_bounded(ptr(markers), ptr(vertices), ptr(fm), F, M, V, ptr(bound),
+                                                          ptr(acc), stream_ptr(dev)))
+    return acc
+
+
 def mean_argmin(acc: torch.Tensor, count: float) -> torch.Tensor:
     acc = _req(acc, "acc")
     M, V = acc.shape
