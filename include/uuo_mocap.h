@@ -77,6 +77,19 @@ int uuo_lbs_forward(const uuo_model* m, const float* betas, int betas_rows, cons
 /* g_vertices[F,V,3] / g_joints[F,J+NE,3] may be NULL (treated as zero).  Outputs (any may be NULL):
  * g_betas[betas_rows,NB], g_global_orient / g_body_pose (shape of the inputs), g_yaw[F], g_transl[F,3].
  * Inputs of the forward call must be passed again unchanged. */
+/* lbs() forward that allocates NOTHING and takes no workspace (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, results and errors as uuo_lbs_forward; the workspace is a file-scope
+ * device array of UUO_STATIC_WORKSPACE_BYTES (8 MiB, held by every GPU that loads the library until the process
+ * exits), which is enough for uuo_lbs_workspace_bytes(m, F) of about 40 frames of an SMPL-sized model; a larger F is
+ * rejected with UUO_ERR_ARG and a message that states both sizes.  The model's device must be current.  Every call
+ * shares that array (it keeps the previous call's contents; the forward writes each region before reading it, so
+ * nothing needs clearing): calls that overlap on one GPU race, serialise them on one stream.  A uuo_lbs_backward on
+ * the same frames needs a caller-allocated workspace and uuo_lbs_forward. */
+#define UUO_STATIC_WORKSPACE_BYTES (8u << 20)
+int uuo_lbs_forward_static(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
+                           const float* body_pose, int pose_mode, const float* yaw, const float* transl, int F,
+                           float* vertices, float* joints, void* stream);
 int uuo_lbs_backward(const uuo_model* m, const float* betas, int betas_rows, const float* global_orient,
                      const float* body_pose, int pose_mode, const float* yaw, int F,
                      const float* g_vertices, const float* g_joints, void* workspace,

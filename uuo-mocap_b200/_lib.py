@@ -25,6 +25,7 @@ SIGNATURES = {
     "uuo_model_info": (_I, [_P, _I]),
     "uuo_lbs_workspace_bytes": (_SZ, [_P, _I]),
     "uuo_lbs_forward": (_I, [_P, _P, _I, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P]),
+    "uuo_lbs_forward_static": (_I, [_P, _P, _I, _P, _P, _I, _P, _P, _I, _P, _P, _P]),
     "uuo_lbs_backward": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "uuo_lbs_backward_rows": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "uuo_lbs_backward_rows_cached": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
