@@ -547,7 +547,8 @@ def run_fit(args, rank, world, local, dev, light=False):
         fitm.optim_chamfer(mk, pose, opose, bt, o_betas, rt, tr, None, None, smpl, cfg, problem=p, groups=groups)
         mark("optim_chamfer")
         if groups == 1:
-            vi = fitm.compute_nearest_points(mk, pose, bt, rt, tr, smpl, config=cfg, shard=shard_fit, as_one_hot=False)
+            vi = fitm.compute_nearest_points(mk, pose, bt, rt, tr, smpl, config=cfg, shard=shard_fit, as_one_hot=False,
+                                                 problem=p)
         else:
             vi = vidx
         mark("compute_nearest_points")

@@ -483,11 +483,12 @@ def optim_markers(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
 def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_inference, marker_labels=None,
                            granularity: str = "full", img_mask=None, device=None, config: Optional[Dict] = None,
                            o_pose_body=None, window_size: int = 1, use_velocity: bool = True,
-                           shard: Optional[Shard] = None, as_one_hot: bool = True):
+                           shard: Optional[Shard] = None, as_one_hot: bool = True, problem: Optional[FitProblem] = None):
     """optimization.py:402-642.  The shipped ``use_mean: True`` branch (:422-430,464-486,595-603): SMPL forward with the
     mean betas, mean over the frames with img_mask == 1 of the marker-vertex distances, argmin.  ``use_mean: False``:
     per-frame ``closest_point`` (see ``_closest_point_last_frames``).  ``use_barycentric`` (igl / trimesh) is not taken.
-    Returns the [M,V] one-hot matrix like the reference (or the index vector)."""
+    Returns the [M,V] one-hot matrix like the reference (or the index vector).  ``problem``: reuse that FitProblem's
+    vertex buffer and workspace (the stages before and after hold them anyway) instead of allocating [F,V,3] again."""
     use_mean = True
     if config is not None:
         cl = config["stages"].get("compute_locations", {})
@@ -505,8 +506,13 @@ def compute_nearest_points(markers, pose_body, betas, root_orient, trans, smpl_i
     mk = markers.to(dev, torch.float32).contiguous()
     F, M = mk.shape[:2]
     mean_betas = torch.mean(betas.to(dev, torch.float32).reshape(-1, mh.NB), dim=0, keepdim=True).contiguous()   # :424
-    vertices = torch.empty((F, mh.V, 3), dtype=torch.float32, device=dev)
-    ws = mh.workspace(F)
+    if problem is not None and problem.F == F and problem.dev == dev and problem.mh.V == mh.V:
+        if problem.vertices is None:
+            problem.vertices = torch.empty((F, mh.V, 3), dtype=torch.float32, device=dev)
+        vertices, ws = problem.vertices, problem.ws
+    else:
+        vertices = torch.empty((F, mh.V, 3), dtype=torch.float32, device=dev)
+        ws = mh.workspace(F)
     pose = pose_body.detach().to(dev, torch.float32).contiguous()
     root = root_orient.detach().to(dev, torch.float32).contiguous()
     tr = trans.detach().to(dev, torch.float32).contiguous()
