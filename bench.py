@@ -360,27 +360,38 @@ def fit_parity_sample(prob, pb, root_d, cap, lo, model, n_sample=64, check=True)
     pose = pb.views["pose_body"][st].cpu().clone().requires_grad_(True)
     trans = pb.views["trans"][st].cpu().clone().requires_grad_(True)
     z = pb.views["z_angle"][st].cpu().clone().reshape(-1, 1, 1).requires_grad_(True)
-    betas = pb.views["betas"].cpu().clone().reshape(1, -1)
+    G = prob.groups                                       # stacked hypotheses: one betas row and one normaliser per group
+    betas_all = pb.views["betas"].cpu().clone().reshape(G, -1)
+    grp = sel // (F // G)
     root = root_d[st].cpu()
     mk = prob.markers[st].cpu()
     orc = OracleSMPL.from_model(model)
     torch.set_num_threads(os.cpu_count() or 1)
-    loss = closures.chamfer_stage_loss(orc, mk, pose, pose.detach(), betas, betas, root, trans, z, {"full_chamfer": 10.0})
-    loss.backward()
-    with torch.no_grad():
-        zr = p3d.compute_root_orient_z(z) @ root
-        v_ref = orc.smpl_inference(p3d.normalize_rot(pose), betas.repeat(len(sel), 1), p3d.normalize_rot(zr), trans)["vertices"]
+    # the oracle normalises by the weight sum of the frames it is given, the run by the group's global one
+    scale = torch.ones(len(sel))
+    v_ref = torch.empty((len(sel), prob.mh.V, 3))
+    for g in np.unique(grp):
+        w = torch.from_numpy(np.where(grp == g)[0])
+        bg = betas_all[g:g + 1]
+        loss = closures.chamfer_stage_loss(orc, mk[w], pose[w], pose[w].detach(), bg, bg, root[w], trans[w], z[w],
+                                           {"full_chamfer": 10.0})
+        loss.backward()
+        scale[w] = float(mask[w].sum()) / prob.wsum_global
+        with torch.no_grad():
+            zr = p3d.compute_root_orient_z(z[w]) @ root[w]
+            v_ref[w] = orc.smpl_inference(p3d.normalize_rot(pose[w]), bg.repeat(len(w), 1), p3d.normalize_rot(zr),
+                                          trans[w])["vertices"]
     per_frame = lambda a, b: float((np.abs(a - b).reshape(len(sel), -1).max(1)
                                     / np.maximum(np.abs(b).reshape(len(sel), -1).max(1), 1e-30)).max())
     v_err = per_frame(v_gpu.numpy(), v_ref.numpy())
     _, idx_ref = p3d.knn_k1(mk, v_gpu)                   # the oracle's argmin on the SAME vertices: must agree exactly
     on = mask != 0
     idx_ok = bool(torch.equal(idx_gpu[on], idx_ref[on]))
-    # the oracle normalised by the sample's weight sum, the run by the global one
-    scale = float(mask.sum()) / prob.wsum_global
     rel = lambda a, b: float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
-    g_err = max(rel(g_gpu["pose_body"], pose.grad.numpy() * scale), rel(g_gpu["trans"], trans.grad.numpy() * scale),
-                rel(g_gpu["z_angle"], z.grad.numpy().reshape(-1) * scale))
+    sc = scale.numpy()
+    g_err = max(rel(g_gpu["pose_body"], pose.grad.numpy() * sc.reshape(-1, 1, 1, 1)),
+                rel(g_gpu["trans"], trans.grad.numpy() * sc.reshape(-1, 1)),
+                rel(g_gpu["z_angle"], z.grad.numpy().reshape(-1) * sc))
     return {"frames_checked": int(len(sel)), "of_frames": int(F), "vertices_rel_err_per_frame": v_err, "vertices_tol": 1e-5,
             "idx_bit_exact": idx_ok, "markers_compared": int(on.sum()), "grad_rel_err": g_err, "grad_tol": 1e-4,
             "ok": bool(v_err < 1e-5 and idx_ok and g_err < 1e-4),

@@ -309,14 +309,14 @@ def test_rows_paths_match_dense_path(get_model, kind, shared, R, F):
                                              int(shared), R, ptr(g_rows), None, ptr(ws), ptr(g[0]), ptr(g[1]),
                                              ptr(g[2]), None, ptr(g[3]), st))
         outs["cached_from_dense"] = g
-        if shared:   # the shared-rows kernel (Bt rows in smem, sparse weights) adds in the order of the per-frame kernel
+        if shared:   # shared rows on the tensor cores (rows_tc.cu, 3xTF32 GEMMs) against the per-frame fp32 kernel
             g2 = grads()
             per_frame = rows_f.to(torch.int32).contiguous()
             check(L.uuo_lbs_backward_rows_cached(mh.handle, ptr(betas), 1, ptr(go), ptr(bp), POSE_RAW6D, None, F,
                                                  ptr(per_frame), 0, R, ptr(g_rows), None, ptr(ws), ptr(g2[0]), ptr(g2[1]),
                                                  ptr(g2[2]), None, ptr(g2[3]), st))
             for a, b in zip(g, g2):
-                assert torch.equal(a, b)
+                assert rel_err(a.cpu().numpy(), b.cpu().numpy()) < 1e-5
     for name, g in outs.items():
         if name == "dense":
             continue

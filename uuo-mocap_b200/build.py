@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libuuomocap.so")
-SOURCES = ["model.cu", "devcfg.cu", "fk.cu", "gemm.cu", "umma_gemm.cu", "skin.cu", "skin_tc.cu", "skin_bwdA_tc.cu", "rows.cu", "nn.cu", "nn_tiles.cu", "fit.cu", "peer.cu", "metrics.cu", "api.cu", "static_ws.cu", "prof.cu"]
+SOURCES = ["model.cu", "devcfg.cu", "fk.cu", "gemm.cu", "umma_gemm.cu", "skin.cu", "skin_tc.cu", "skin_bwdA_tc.cu", "rows.cu", "rows_tc.cu", "nn.cu", "nn_tiles.cu", "fit.cu", "peer.cu", "metrics.cu", "api.cu", "static_ws.cu", "prof.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -15,6 +15,8 @@
 #define UUO_SKIN_J 24      // the dense skinning kernels are compiled for the SMPL joint count
 #define UUO_NSPLIT_GA 4    // vertex splits of the skinning-backward dA reduction (deterministic partials)
 #define UUO_NSPLIT_GC 16   // K splits of the posedirs-transpose GEMM (deterministic partials)
+#define UUO_SEL_LD 192     // 3 R <= 192 selected row coordinates per frame (R <= 64)
+#define UUO_SEL_IMG_FLOATS (8 * 2 * 192 * 32 + 6 * 2 * 256 * 32 + 192 + 3 * 64 * 24 + 3 * 24 * 64 + 256)
 #define UUO_GA_STRIDE 292  // 288 dA entries + 3 (sum_v g_v) + 1 pad
 
 struct uuo_model {
@@ -81,8 +83,15 @@ struct uuo_ws {
   float* rowbuf;  // [F][R<=64][4]  scratch of the row-sparse paths
   float* Aimg;    // [ceil(F/16)][2][192*32] tf32 hi|lo swizzled image of the relative transforms (skin_tc.cu)
   float* vshaped; // [NP]  v_template + shapedirs . betas when ONE betas row is shared by all frames (exact fp32)
+  // rows shared by all frames on the tensor cores (rows_tc.cu)
+  float* sel_vp;   // [F][UUO_SEL_LD]  v_posed of the selected rows (3r + c), columns >= 3R are padding
+  float* sel_gvp;  // [F][UUO_SEL_LD]  d v_posed of the selected rows, padding columns written as 0
+  float* sel_img;  // [uuo_sel_images(F)][UUO_SEL_IMG_FLOATS] per row group: both operand images + bias + sparse weight tables of the current row set
   size_t total_floats;
 };
+
+// operand images of selected row sets the workspace holds: one per row group of >= 64 frames, at most 64
+static inline int uuo_sel_images(int F) { return F < 128 ? 1 : (F / 64 > 64 ? 64 : F / 64); }
 
 static inline size_t align4(size_t x) { return (x + 3) & ~(size_t)3; }
 
@@ -103,6 +112,9 @@ static inline uuo_ws carve_ws(const uuo_model* m, int F, void* base) {
   w.rowbuf = take((size_t)F * 64 * 4);
   w.Aimg = take((size_t)((F + 15) / 16) * 2 * 192 * 32);
   w.vshaped = take((size_t)m->NP);
+  w.sel_vp = take((size_t)F * UUO_SEL_LD);
+  w.sel_gvp = take((size_t)F * UUO_SEL_LD);
+  w.sel_img = take((size_t)uuo_sel_images(F) * UUO_SEL_IMG_FLOATS);
   w.total_floats = off;
   return w;
 }
@@ -176,6 +188,13 @@ int uuo_gcoef_splits(const uuo_model* m, int F);
 int launch_pack_transforms(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st);
 int launch_skin_tc(const uuo_model* m, int mode, int F, const float* in, const float* g_joints, const float* transl,
                    float* out, const uuo_ws& ws, cudaStream_t st);
+int launch_umma_one_tile(const float* A, long lda, int M, const float* Bimg, int NT, int kb_total, const float* bias,
+                         float* C, long ldc, int groups, long b_group_stride, long bias_group_stride, cudaStream_t st);
+bool rows_tc_usable(const uuo_model* m, int F, int rows_shared, int R);
+int launch_rows_forward_tc(const uuo_model* m, const float* transl, int F, const int32_t* rows, int G, int R,
+                           float* out_rows, const uuo_ws& ws, cudaStream_t st);
+int launch_rows_backward_tc(const uuo_model* m, int F, const int32_t* rows, int G, int R, const float* g_rows,
+                            const uuo_ws& ws, cudaStream_t st);
 int launch_skin_bwdA_tc(const uuo_model* m, int F, const float* g_vertices, const float* g_joints, const uuo_ws& ws,
                         cudaStream_t st);
 int uuo_bwdA_splits(const uuo_model* m);

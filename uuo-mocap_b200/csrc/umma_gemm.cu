@@ -47,7 +47,25 @@ struct GemmArgs {
   int m_group;                       // m tiles per group of the item order (see decode_item)
   int terms;                         // 3: Ahi.Bhi + Alo.Bhi + Ahi.Blo;  2: B's lo half is neither fetched nor multiplied
   int k_zero_from;                   // columns k >= this of A are read as 0 (-1: none)
+  // row GROUPS (rows_tc.cu, stacked hypotheses): group_rows > 0 = consecutive blocks of that many rows of A / C, each
+  // with its own B image and bias; an m tile never straddles two groups (mt_per_group tiles per group, the last ragged)
+  int group_rows, mt_per_group;
+  long b_group_stride, bias_group_stride;
 };
+
+// rows of an m tile: first global row, and how many rows from `local` on are real
+__device__ __forceinline__ void tile_rows(const GemmArgs& g, int mt, int local, long& row, int& nreal, int& grp) {
+  if (g.group_rows > 0) {
+    grp = mt / g.mt_per_group;
+    const int rl = (mt - grp * g.mt_per_group) * BM + local;
+    row = (long)grp * g.group_rows + rl;
+    nreal = g.group_rows - rl;
+  } else {
+    grp = 0;
+    row = (long)mt * BM + local;
+    nreal = g.M - (int)row;
+  }
+}
 
 // Work item w -> (m tile, n tile, k split).  m tiles are walked in GROUPS of g.m_group: inside a group the CTAs sweep
 // all its m tiles for one n tile, then the next n tile, ... so the A rows of the group (m_group x 128 rows) are re-read
@@ -115,9 +133,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int q = tp + 256 * i, row = q >> 3, c = q & 7;
-        const int gr = mt * BM + row;
+        long gr;
+        int nreal, grp;
+        tile_rows(g, mt, row, gr, nreal, grp);
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gr < g.M) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + (long)gr * g.lda + (long)kb * BK + c * 4));
+        if (nreal > 0) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + gr * g.lda + (long)kb * BK + c * 4));
         if (g.k_zero_from >= 0) {
           const int k0 = kb * BK + c * 4;
           if (k0 + 3 >= g.k_zero_from) {
@@ -184,7 +204,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
           umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
           const uint32_t nbytes = (TERMS == 3 ? 2u : 1u) * b_tile_bytes;       // hi | lo are contiguous: hi alone = first half
           umma::mbar_arrive_expect_tx(FULL_B(s), nbytes);
-          const float* src = g.Bimg + ((size_t)nt * g.kb_total + kb) * (size_t)(2 * g.NT * BK);
+          const float* src = g.Bimg + ((size_t)nt * g.kb_total + kb) * (size_t)(2 * g.NT * BK) +
+                             (g.group_rows > 0 ? (size_t)(mt / g.mt_per_group) * g.b_group_stride : 0);
           umma::bulk_g2s(base + s * STAGE_BYTES + 2 * A_TILE_BYTES, src, nbytes, FULL_B(s));
         }
       }
@@ -234,8 +255,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
       umma::mbar_wait(TFULL(acc), (item >> 1) & 1);
       umma::tc_fence_after();
       float* Cw = g.C + (size_t)ks * g.split_stride;
-      const int row0 = mt * BM + warp * 32;
-      const int nrows = min(32, g.M - row0);   // may be <= 0 for a ragged last tile
+      long row0;
+      int nreal, grp;
+      tile_rows(g, mt, warp * 32, row0, nreal, grp);
+      const int nrows = min(32, nreal);        // may be <= 0 for a ragged last tile
       const int sub = lane >> 3, c4 = lane & 7;
       for (int c = 0; c < g.NT / 32; ++c) {
         uint32_t r[32];
@@ -251,7 +274,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         const int col = nt * g.NT + c * 32 + c4 * 4;
         if (col < g.n_valid) {
           float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (g.bias) bv = __ldg(reinterpret_cast<const float4*>(g.bias + col));
+          if (g.bias) bv = __ldg(reinterpret_cast<const float4*>(g.bias + (size_t)grp * g.bias_group_stride + col));
           float* dst = Cw + (size_t)row0 * g.ldc + col;
 #pragma unroll
           for (int rr = 0; rr < 8; ++rr) {
@@ -356,6 +379,7 @@ int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, bool be
   g.Bimg = m->Bimg_fwd;
   g.C = ws.vposed; g.ldc = m->NP; g.split_stride = 0;
   g.bias = m->vt; g.terms = 3; g.k_zero_from = -1;
+  g.group_rows = 0; g.mt_per_group = 1; g.b_group_stride = 0; g.bias_group_stride = 0;
   if (betas_shared) {
     // betas are shared by all frames (the fitting loop, optimization.py:196-202): the shape blend is frame independent,
     // so it is evaluated once in exact fp32 and enters as the bias; the tensor cores see only the pose rows, where the
@@ -369,12 +393,35 @@ int launch_vposed_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, bool be
   return launch_umma(g, st);
 }
 
+// C[M][ldc] = A[M][lda] . B^T (+ bias) for ONE n tile of NT columns (a multiple of 32, <= 256) whose 3xTF32 image
+// [kb_total][2][NT*32] the caller built (rows_tc.cu: the selected rows of the marker stage); K = 32 kb_total.
+// groups > 1: M = groups x (M / groups) rows, group g uses the image at Bimg + g b_group_stride (bias likewise)
+int launch_umma_one_tile(const float* A, long lda, int M, const float* Bimg, int NT, int kb_total, const float* bias,
+                         float* C, long ldc, int groups, long b_group_stride, long bias_group_stride, cudaStream_t st) {
+  GemmArgs g;
+  g.A = A; g.lda = lda; g.M = M;
+  g.Bimg = Bimg;
+  g.C = C; g.ldc = ldc; g.split_stride = 0;
+  g.bias = bias; g.terms = 3; g.k_zero_from = -1;
+  g.NT = NT; g.n_tiles = 1; g.m_tiles = (M + BM - 1) / BM;
+  g.group_rows = 0; g.mt_per_group = 1; g.b_group_stride = 0; g.bias_group_stride = 0;
+  if (groups > 1) {
+    g.group_rows = M / groups;
+    g.mt_per_group = (g.group_rows + BM - 1) / BM;
+    g.m_tiles = groups * g.mt_per_group;
+    g.b_group_stride = b_group_stride; g.bias_group_stride = bias_group_stride;
+  }
+  g.kb_total = kb_total; g.k_splits = 1; g.kb_per_split = kb_total; g.n_valid = NT;
+  return launch_umma(g, st);
+}
+
 int launch_gcoef_gemm_umma(const uuo_model* m, int F, const uuo_ws& ws, cudaStream_t st) {
   GemmArgs g;
   g.A = ws.gvposed; g.lda = m->NP; g.M = F;
   g.Bimg = m->Bimg_bwd;
   g.C = ws.gcoef; g.ldc = m->KP; g.split_stride = (long)F * m->KP;
   g.bias = nullptr; g.terms = 3; g.k_zero_from = -1;
+  g.group_rows = 0; g.mt_per_group = 1; g.b_group_stride = 0; g.bias_group_stride = 0;
   g.NT = m->KP; g.n_tiles = 1; g.m_tiles = (F + BM - 1) / BM;
   g.kb_total = m->NP / BK; g.k_splits = uuo_gcoef_splits(m, F);
   g.kb_per_split = (g.kb_total + g.k_splits - 1) / g.k_splits; g.n_valid = m->KP;
