@@ -405,6 +405,15 @@ def rot_z(angle: torch.Tensor) -> torch.Tensor:
     return torch.stack([c, -s, z, s, c, z, z, z, o], dim=-1).reshape(angle.shape[:-1] + (3, 3))
 
 
+def rot_z_apply(angle: torch.Tensor, m: torch.Tensor) -> torch.Tensor:
+    """rot_z(angle) @ m written out row by row (Rz only mixes rows 0 and 1): elementwise kernels instead of a batched
+    library GEMM of 3x3 matrices.  angle [...,1], m [...,3,3] (broadcast against each other)."""
+    c, s = torch.cos(angle[..., 0])[..., None], torch.sin(angle[..., 0])[..., None]
+    r0, r1, r2 = m[..., 0, :], m[..., 1, :], m[..., 2, :]
+    a, b = c * r0 - s * r1, s * r0 + c * r1
+    return torch.stack((a, b, r2.expand_as(a)), dim=-2)
+
+
 def normalize_rot(m: torch.Tensor) -> torch.Tensor:
     """multimodal.py:34-35 (6D round trip) for the final packing step -- small torch ops on the device."""
     a1, a2 = m[..., 0, :], m[..., 1, :]
@@ -441,7 +450,7 @@ def optim_chamfer(markers, pose_body, o_pose_body, betas, o_betas, root_orient, 
         betas.copy_(pb.views["betas"].view_as(betas))
         pose_body.copy_(pb.views["pose_body"])
         if yaw_lock:
-            root_orient.copy_(rot_z(pb.views["z_angle"].view(F, 1, 1)) @ root)      # :280-281
+            root_orient.copy_(rot_z_apply(pb.views["z_angle"].view(F, 1, 1), root))  # :280-281
         else:
             root_orient.copy_(normalize_rot(pb.views["z_angle"]) @ root)            # :282-283
     return prob
@@ -637,7 +646,7 @@ def fit_hypotheses(markers, pose_body, o_pose_body, betas, o_betas, root_orient,
     mk, opose = rep(markers), rep(o_pose_body)
     pose, tr = rep(pose_body), rep(trans)
     ang = torch.as_tensor(list(angles), dtype=torch.float32, device=dev)
-    root = (rot_z(ang.view(H, 1, 1, 1)) @ T(root_orient).unsqueeze(0)).reshape(H * F, 1, 3, 3).contiguous()   # :465
+    root = rot_z_apply(ang.view(H, 1, 1, 1), T(root_orient).unsqueeze(0)).reshape(H * F, 1, 3, 3).contiguous()   # :465
     bet = T(betas).reshape(1, -1).repeat(H, 1).contiguous()
     obet = T(o_betas).reshape(1, -1)
     lbfgs = str(config.get("optimizer", {}).get("name", "lbfgs")).lower() == "lbfgs"
