@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
                 float* o = a.out + ((size_t)f * a.V + v) * 3;
 #pragma unroll
                 for (int rr = 0; rr < 3; ++rr)
-                  o[rr] = (T[rr * 4] * x[k][0] + T[rr * 4 + 1] * x[k][1] + T[rr * 4 + 2] * x[k][2] + T[rr * 4 + 3]) + tr[rr];
+                  __stcs(o + rr, (T[rr * 4] * x[k][0] + T[rr * 4 + 1] * x[k][1] + T[rr * 4 + 2] * x[k][2] + T[rr * 4 + 3]) + tr[rr]);   // streamed
               }
             } else {
               // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads

@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
             const int rl = rr * 4 + sub;     // 4 rows per instruction, 8 lanes x 16 B = one 128 B line per row
             float4 v = *reinterpret_cast<const float4*>(stg + rl * 32 + ((c4 ^ (rl & 7)) << 2));
             v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-            if (rl < nrows) *reinterpret_cast<float4*>(dst + (size_t)rl * g.ldc) = v;
+            if (rl < nrows) __stcs(reinterpret_cast<float4*>(dst + (size_t)rl * g.ldc), v);   // streamed: keep A / B in L2
           }
         }
         __syncwarp();
@@ -336,7 +336,7 @@ void uuo_build_b_image(std::vector<float>& out, const float* src, int rows, int 
 static int launch_umma(GemmArgs g, cudaStream_t st) {
   const int items = g.m_tiles * g.n_tiles * g.k_splits;
   const int grid = std::min(items, uuo_sm_count());
-  g.m_group = std::min(g.m_tiles, 2 * grid);               // <= 296 m tiles = 34 MB of fp32 rows at K = 224
+  g.m_group = std::min(g.m_tiles, 2 * grid);               // <= 296 m tiles = 34 MB of fp32 rows at K = 224 (1x and 4x: slower)
   if (g.terms == 2) {
     UUO_DYN_SMEM(umma_gemm_kernel<2>, smem_bytes<2>());
     umma_gemm_kernel<2><<<grid, NTHREADS, smem_bytes<2>(), st>>>(g);
