@@ -129,7 +129,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
     int w = blockIdx.x, mt = 0, nt = 0, ks = 0, kb = 0, kb_end = 0;
     bool live = w < n_items;
     if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
-    auto gload = [&](float4 (&v)[4]) {   // loads the block the iterator points at, then advances it
+    auto gload = [&](float4 (&v)[4], int& kb_of) {   // loads the block the iterator points at, then advances it
+      kb_of = kb;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int q = tp + 256 * i, row = q >> 3, c = q & 7;
@@ -138,15 +139,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         tile_rows(g, mt, row, gr, nreal, grp);
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (nreal > 0) v[i] = __ldg(reinterpret_cast<const float4*>(g.A + gr * g.lda + (long)kb * BK + c * 4));
-        if (g.k_zero_from >= 0) {
-          const int k0 = kb * BK + c * 4;
-          if (k0 + 3 >= g.k_zero_from) {
-            if (k0 >= g.k_zero_from) v[i].x = 0.f;
-            if (k0 + 1 >= g.k_zero_from) v[i].y = 0.f;
-            if (k0 + 2 >= g.k_zero_from) v[i].z = 0.f;
-            v[i].w = 0.f;
-          }
-        }
       }
       if (++kb >= kb_end) {
         w += gridDim.x;
@@ -154,14 +146,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
         if (live) { decode_item(g, w, mt, nt, ks); kb = ks * g.kb_per_split; kb_end = min(kb + g.kb_per_split, g.kb_total); }
       }
     };
-    float4 buf[PF][4], nw[4];
     uint32_t loaded = 0, it = 0;
-#pragma unroll
-    for (int d = 0; d < PF; ++d)
-      if (live) { gload(buf[d]); ++loaded; }
-    while (it < loaded) {
-      const bool more = live;
-      if (more) { gload(nw); ++loaded; }
+    // split + store one block.  Nothing touches the loaded registers before this point: the k_zero_from masking used
+    // to sit in gload, right behind the __ldg, so every load was waited for at once and the prefetch distance was lost
+    // (ncu source page: 24 % of the kernel's stall samples on that line)
+    auto consume = [&](float4 (&v)[4], int kb_of) {
       const int s = it % STAGES;
       umma::mbar_wait(EMPTY(s), ((it / STAGES) & 1) ^ 1);
       uint8_t* a_hi = sm + s * STAGE_BYTES;
@@ -170,27 +159,50 @@ __global__ void __launch_bounds__(NTHREADS, 1) umma_gemm_kernel(const GemmArgs g
       for (int i = 0; i < 4; ++i) {
         const int q = tp + 256 * i, row = q >> 3, c = q & 7;
         const int off = row * 128 + ((c ^ (row & 7)) << 4);
+        float4 x = v[i];
+        if (g.k_zero_from >= 0) {
+          const int k0 = kb_of * BK + c * 4;
+          if (k0 + 3 >= g.k_zero_from) {
+            if (k0 >= g.k_zero_from) x.x = 0.f;
+            if (k0 + 1 >= g.k_zero_from) x.y = 0.f;
+            if (k0 + 2 >= g.k_zero_from) x.z = 0.f;
+            x.w = 0.f;
+          }
+        }
         float4 h, l;
-        umma::split_tf32(buf[0][i].x, h.x, l.x);
-        umma::split_tf32(buf[0][i].y, h.y, l.y);
-        umma::split_tf32(buf[0][i].z, h.z, l.z);
-        umma::split_tf32(buf[0][i].w, h.w, l.w);
+        umma::split_tf32(x.x, h.x, l.x);
+        umma::split_tf32(x.y, h.y, l.y);
+        umma::split_tf32(x.z, h.z, l.z);
+        umma::split_tf32(x.w, h.w, l.w);
         *reinterpret_cast<float4*>(a_hi + off) = h;
         *reinterpret_cast<float4*>(a_lo + off) = l;
       }
       umma::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) umma::mbar_arrive(FULL_A(s));
-#pragma unroll
-      for (int d = 0; d + 1 < PF; ++d)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) buf[d][i] = buf[d + 1][i];
-      if (more) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) buf[PF - 1][i] = nw[i];
-      }
       ++it;
+    };
+    // a ring of PF + 1 register buffers with STATIC roles (the loop is unrolled over the ring): slot C is consumed while
+    // slot L receives the block PF ahead; no register moves, so a load is first waited for PF blocks after its issue
+    float4 b0[4], b1[4], b2[4], b3[4];
+    int k0_ = 0, k1_ = 0, k2_ = 0, k3_ = 0;
+    static_assert(PF == 3, "the ring below is written for PF = 3");
+    if (live) { gload(b0, k0_); ++loaded; }
+    if (live) { gload(b1, k1_); ++loaded; }
+    if (live) { gload(b2, k2_); ++loaded; }
+#define UUO_GEMM_STEP(C, KC, L, KL)                        \
+    {                                                      \
+      if (it >= loaded) break;                             \
+      if (live) { gload(L, KL); ++loaded; }                \
+      consume(C, KC);                                      \
     }
+    while (true) {
+      UUO_GEMM_STEP(b0, k0_, b3, k3_)
+      UUO_GEMM_STEP(b1, k1_, b0, k0_)
+      UUO_GEMM_STEP(b2, k2_, b1, k1_)
+      UUO_GEMM_STEP(b3, k3_, b2, k2_)
+    }
+#undef UUO_GEMM_STEP
   } else if (warp == WARP_BLOAD) {
     // ===== B loader: one bulk copy per stage brings the pre-swizzled (hi|lo) tile =====
     if (lane == 0) {
