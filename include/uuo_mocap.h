@@ -81,7 +81,7 @@ int uuo_lbs_forward(const uuo_model* m, const float* betas, int betas_rows, cons
  * the run's operators, for callers that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, results and errors as uuo_lbs_forward; the workspace is a file-scope
  * device array of UUO_STATIC_WORKSPACE_BYTES (8 MiB, held by every GPU that loads the library until the process
- * exits), which is enough for uuo_lbs_workspace_bytes(m, F) of about 40 frames of an SMPL-sized model; a larger F is
+ * exits), which is enough for uuo_lbs_workspace_bytes(m, F) of about 35 frames of an SMPL-sized model; a larger F is
  * rejected with UUO_ERR_ARG and a message that states both sizes.  The model's device must be current.  Every call
  * shares that array (it keeps the previous call's contents; the forward writes each region before reading it, so
  * nothing needs clearing): calls that overlap on one GPU race, serialise them on one stream.  A uuo_lbs_backward on
