@@ -58,6 +58,7 @@ struct uuo_tree {
   int8_t depth[UUO_MAX_J];
   int8_t children[UUO_MAX_J][UUO_MAX_CHILD];
   int J, max_depth;
+  uint8_t slot_mask[UUO_MAX_J + 1];   // per depth d: bit c set when some joint's child slot c holds a joint of depth d
 };
 
 static inline uuo_tree make_tree(const uuo_model* m) {
@@ -67,6 +68,12 @@ static inline uuo_tree make_tree(const uuo_model* m) {
   memcpy(t.children, m->children, sizeof(t.children));
   t.J = m->J;
   t.max_depth = m->max_depth;
+  memset(t.slot_mask, 0, sizeof(t.slot_mask));
+  for (int j = 0; j < m->J; ++j)
+    for (int c = 0; c < UUO_MAX_CHILD; ++c) {
+      const int cj = m->children[j][c];
+      if (cj >= 0) t.slot_mask[m->depth[cj]] |= (uint8_t)(1u << c);
+    }
   return t;
 }
 

@@ -343,6 +343,7 @@ __global__ void __launch_bounds__(128) fk_backward_kernel(
     }
 #pragma unroll
     for (int c = 0; c < UUO_MAX_CHILD; ++c) {
+      if (!((tree.slot_mask[d] >> c) & 1)) continue;      // no joint has a depth-d child in this slot (uniform)
       const int cj = ch[c];
       const bool valid = cj >= 0 && tree.depth[cj >= 0 ? cj : 0] == d;
       const int srcl = valid ? cj : lane;
