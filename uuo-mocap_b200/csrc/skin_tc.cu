@@ -158,12 +158,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
     const uintptr_t in_base = reinterpret_cast<uintptr_t>(a.in) + (size_t)v_first * 12;
     const uintptr_t in_end = reinterpret_cast<uintptr_t>(a.in) + (size_t)a.F * pitch * 4;
     const size_t pitch4 = (size_t)pitch * 4;
-    auto row_shift = [&](int f) { return (uint32_t)((in_base + (size_t)f * pitch * 4) & 15); };
+    // MODE 0 reads v_posed: rows of NP floats (a multiple of 64 B) from a 16 B aligned workspace - no shift, no hull
+    auto row_shift = [&](int f) { return MODE == 0 ? 0u : (uint32_t)((in_base + (size_t)f * pitch * 4) & 15); };
     auto issue = [&](int ft, int stage) {
       if (ft < ft1) {
         const uint32_t dst0 = xw_s + stage * XW_BYTES;
         const int f0 = ft * NF + gq * 8;
         const uintptr_t row0 = in_base + (size_t)f0 * pitch4;
+        if (MODE == 0) {                 // 8 frames x 24 aligned 16 B chunks = 6 per lane
+#pragma unroll
+          for (int i = 0; i < 6; ++i) {
+            const int q = lane + 32 * i, fi = q / 24, ch = q - fi * 24;
+            const bool ok = f0 + fi < a.F;
+            umma::cp_async16(dst0 + fi * XROW + ch * 16,
+                             ok ? reinterpret_cast<const void*>(row0 + (size_t)fi * pitch4 + ch * 16) : (const void*)a.Wimg,
+                             ok ? 16u : 0u);
+          }
+        } else
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
           const int q = lane + 32 * i;
@@ -197,6 +208,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
       __syncwarp();
       umma::mbar_wait(TFULL(acc), (it >> 1) & 1);
       umma::tc_fence_after();
+      // output row of the tile's first frame for this lane's vertex; frames are out_pitch floats apart
+      const size_t out_pitch = MODE == 0 ? (size_t)a.V * 3 : (size_t)a.NP;
+      float* const o_tile = a.out + (size_t)fbase * out_pitch + (size_t)v * 3;
 #pragma unroll
       for (int st = 0; st < 2; ++st) {
         uint32_t r[48];
@@ -222,14 +236,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) skin_tc_kernel(const SkinArgs a) 
             if (MODE == 0) {
               if (v_ok) {
                 const float* tr = xin + 8 * (XROW / 4) + i * 3;   // broadcast read
-                float* o = a.out + ((size_t)f * a.V + v) * 3;
+                float* o = o_tile + (size_t)i * out_pitch;
 #pragma unroll
                 for (int rr = 0; rr < 3; ++rr)
                   __stcs(o + rr, (T[rr * 4] * x[k][0] + T[rr * 4 + 1] * x[k][1] + T[rr * 4 + 2] * x[k][2] + T[rr * 4 + 3]) + tr[rr]);   // streamed
               }
             } else {
               // vertex slots past V have zero weights -> zeros, which also clears the row padding the GEMM reads
-              float* o = a.out + (size_t)f * a.NP + (size_t)v * 3;
+              float* o = o_tile + (size_t)i * out_pitch;
               const float g0 = x[k][0], g1 = x[k][1], g2 = x[k][2];
 #pragma unroll
               for (int c = 0; c < 3; ++c) o[c] = T[c] * g0 + T[4 + c] * g1 + T[8 + c] * g2;
