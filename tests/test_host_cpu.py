@@ -277,3 +277,33 @@ def test_bench_reference_arm_line(tmp_path):
         os.close(saved[0])
     want = bench.fit_config(argparse.Namespace(workload="fit100k", frames=0), 1)
     assert d["config"] == want and "configs[4]" in d["config"]["workload"]
+
+
+def test_rot_z_apply_equals_matmul():
+    """fit.rot_z_apply (elementwise Rz @ m, used for the yaw write-back and the stacked hypotheses) == rot_z(angle) @ m."""
+    from uuo_mocap_b200 import fit
+    g = torch.Generator().manual_seed(3)
+    z, R = torch.randn(7, 1, 1, generator=g), torch.randn(7, 1, 3, 3, generator=g)
+    assert torch.allclose(fit.rot_z_apply(z, R), fit.rot_z(z) @ R, atol=1e-6)
+    ang = torch.randn(3, generator=g)
+    a = fit.rot_z(ang.view(3, 1, 1, 1)) @ R.unsqueeze(0)
+    b = fit.rot_z_apply(ang.view(3, 1, 1, 1), R.unsqueeze(0))
+    assert a.shape == b.shape and torch.allclose(a, b, atol=1e-6)
+
+
+def test_mean_bound_covers_the_in_order_fp32_sum():
+    """ops.mean_bound_from_sums: the fp32 bound built from an fp64 sum is >= the in-order fp32 sum of the same
+    non-negative terms (what uuo_mean_dist_accumulate_bounded compares its running sums with)."""
+    from uuo_mocap_b200 import ops
+    rng = np.random.default_rng(0)
+    for n in (1, 7, 1000, 200000):
+        x = np.abs(rng.normal(0.3, 0.2, size=(5, n))).astype(np.float32)
+        s32 = np.zeros(5, dtype=np.float32)
+        for k in range(n if n <= 1000 else 0):
+            s32 = s32 + x[:, k]
+        if n > 1000:
+            s32 = np.cumsum(x, axis=1, dtype=np.float32)[:, -1]          # sequential fp32 accumulation
+        s64 = torch.from_numpy(x.astype(np.float64).sum(1))
+        b = ops.mean_bound_from_sums(s64, n).numpy()
+        rel = 2.0 ** -10 + n * 2.0 ** -23                                 # the margin mean_bound_from_sums adds
+        assert b.dtype == np.float32 and (b >= s32).all() and (b <= s64.numpy() * (1 + 1.01 * rel) + 1e-6).all()
