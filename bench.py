@@ -537,7 +537,7 @@ def run_fit(args, rank, world, local, dev, light=False):
     cfg["stages"]["chamfer"]["losses"], cfg["stages"]["marker"]["losses"] = dict(loss_ch), dict(loss_mk)
     pin = lambda x: x.clone().pin_memory()
     h = {"markers": pin(markers), "pose": pin(o_pose), "root": pin(root), "trans": pin(trans), "betas": pin(betas0)}
-    h2d = sum(x.numel() * 4 for x in h.values()) + h["pose"].numel() * 4
+    h2d = sum(x.numel() * 4 for x in h.values())
     d2h = sum(h[k].numel() * 4 for k in ("pose", "root", "trans", "betas"))
     h_out = {k: torch.empty_like(h[k]).pin_memory() for k in ("pose", "root", "trans", "betas")}
     del prob, pb_ch, pb_mk, state, graphs
@@ -550,7 +550,8 @@ def run_fit(args, rank, world, local, dev, light=False):
                 marks.append((name, time.perf_counter()))
         mark("start")
         mk = h["markers"].to(dev, non_blocking=True)
-        pose, opose = h["pose"].to(dev, non_blocking=True), h["pose"].to(dev, non_blocking=True)
+        pose = h["pose"].to(dev, non_blocking=True)
+        opose = pose.clone()                      # the prior pose starts as the same tensor (multimodal.py): copied on the device
         rt, tr, bt = (h[k].to(dev, non_blocking=True) for k in ("root", "trans", "betas"))
         mark("h2d")
         p = fitm.FitProblem(smpl, mk, opose, o_betas, shard_fit, groups)

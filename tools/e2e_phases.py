@@ -43,7 +43,8 @@ def once(report):
         marks.append((name, time.perf_counter()))
     mark("start")
     mk = h["markers"].to(dev, non_blocking=True)
-    pose, opose = h["pose"].to(dev, non_blocking=True), h["pose"].to(dev, non_blocking=True)
+    pose = h["pose"].to(dev, non_blocking=True)
+    opose = pose.clone()
     rt, tr = h["root"].to(dev, non_blocking=True), h["trans"].to(dev, non_blocking=True)
     bt = o_betas.reshape(1, -1).to(dev)
     mark("h2d")

@@ -35,7 +35,8 @@ shard = Shard()
 
 def once():
     mk = h["markers"].to(dev, non_blocking=True)
-    pose, opose = h["pose"].to(dev, non_blocking=True), h["pose"].to(dev, non_blocking=True)
+    pose = h["pose"].to(dev, non_blocking=True)
+    opose = pose.clone()
     rt, tr = h["root"].to(dev, non_blocking=True), h["trans"].to(dev, non_blocking=True)
     bt = o_betas.reshape(1, -1).to(dev)
     p = fitm.FitProblem(smpl, mk, opose, o_betas, shard, 1)
