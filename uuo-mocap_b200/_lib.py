@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libuuomocap.so")
+# UUO_MOCAP_LIB: another build of the same library (tools/ab.sh times two builds on one box); the default is the in-tree one
+LIB_PATH = os.environ.get("UUO_MOCAP_LIB") or os.path.join(_HERE, "lib", "libuuomocap.so")
 
 _P = C.c_void_p
 _I = C.c_int
