@@ -278,6 +278,9 @@ def marker_closure(prob: FitProblem, pb: ParamBlock, vertex_idx: torch.Tensor, l
 # ------------------------------------------------------------------------------------------------
 # optimiser drivers
 # ------------------------------------------------------------------------------------------------
+_CAPTURE_STREAMS: Dict[torch.device, "torch.cuda.Stream"] = {}      # device -> side stream of the graph captures
+
+
 def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int, lr: float,
              betas=(0.9, 0.999), eps: float = 1e-8, on_iter: Optional[Callable] = None,
              graph: Optional[bool] = None, warm: int = 3, shard: Optional[Shard] = None) -> Optional[torch.Tensor]:
@@ -312,9 +315,22 @@ def run_adam(pb: ParamBlock, closure: Callable[[], torch.Tensor], num_iters: int
         dev = pb.flat.device
         g = torch.cuda.CUDAGraph()
         with torch.cuda.device(dev):
-            # thread_local: NCCL's watchdog thread may touch the CUDA API while this thread captures
-            with torch.cuda.graph(g, capture_error_mode="thread_local" if multi else "global"):
-                loss = one()
+            # capture_begin / capture_end directly: the torch.cuda.graph context manager first empties the caching
+            # allocator and the pinned-host cache (cudaFree of every idle block: GBs at these sizes, blocking, and the
+            # blocks have to be cudaMalloc'ed again), on every stage of every call
+            side = _CAPTURE_STREAMS.get(dev)
+            if side is None:
+                side = _CAPTURE_STREAMS[dev] = torch.cuda.Stream(dev)
+            cur = torch.cuda.current_stream(dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                # thread_local: NCCL's watchdog thread may touch the CUDA API while this thread captures
+                g.capture_begin(capture_error_mode="thread_local" if multi else "global")
+                try:
+                    loss = one()
+                finally:
+                    g.capture_end()
+            cur.wait_stream(side)
             while it < num_iters:        # the capture itself executed nothing
                 g.replay()
                 it += 1
